@@ -1,0 +1,22 @@
+"""blendtorch.btt -- B200-native ingest path with the reference's surface.
+
+Same public names as pkg_pytorch/blendtorch/btt/__init__.py for the ingest path
+(`RemoteIterableDataset`, `FileDataset`, `FileRecorder`, `FileReader`); the control plane of the
+reference (launcher, duplex channel, gym environments) is out of scope here and not provided.
+New, additive names: `DeviceLoader`, `Preprocess`, `preprocess_images`, `Camera`, `DataPublisher`,
+`shard`.
+"""
+from .constants import DEFAULT_TIMEOUTMS
+from .dataset import FileDataset, RemoteIterableDataset, SingleFileDataset
+from .file import FileReader, FileRecorder
+from . import native
+from .preprocess import Preprocess, preprocess_images
+from .camera import Camera
+from .loader import DeviceLoader, shard
+from .publisher import DataPublisher
+
+__version__ = "0.2.0+b200.1"
+
+__all__ = ["RemoteIterableDataset", "FileDataset", "SingleFileDataset", "FileRecorder", "FileReader",
+           "DeviceLoader", "Preprocess", "preprocess_images", "Camera", "DataPublisher", "shard",
+           "DEFAULT_TIMEOUTMS", "native"]

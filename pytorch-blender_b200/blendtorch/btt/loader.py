@@ -1,0 +1,351 @@
+"""DeviceLoader: batches of training-ready *device* tensors from a btt dataset.
+
+Takes the place of ``torch.utils.data.DataLoader(ds, batch_size, num_workers) + item_transform
++ default_collate + batch.to(device)`` in a reference script (benchmarks/benchmark.py:26-41,
+examples/datagen/generate.py:79-85, examples/densityopt/densityopt.py:210-268):
+
+    ds = btt.RemoteIterableDataset(addresses, max_items=N)          # or btt.FileDataset(prefix)
+    dl = btt.DeviceLoader(ds, batch_size=8, device='cuda:0',
+                          preprocess=btt.Preprocess(gamma=2.2, mean=127.5, std=127.5))
+    for batch in dl:       # dict of CUDA tensors, same keys/dtypes/shapes default_collate gives
+        ...
+
+Pipeline per batch: receiver thread(s) -> `bt_schema_ingest` (one memcpy per payload byte, GIL
+released) into a pinned slot -> one `cudaMemcpyAsync` on the loader's copy stream -> K1 on the
+same stream -> CUDA event; the consumer's stream waits on the event, never the host.  Annotation
+columns (xy, bbox, frameid, btid, depth ...) are views into the per-batch device buffer, so they
+cost no kernel.  Ordering and delivery follow the reference: in order per publisher with one
+receiver, unordered across receivers, every message delivered once
+(examples/datagen/Readme.md:172-177); back-pressure is the bounded queue + ZMQ high-water marks.
+"""
+import queue
+import threading
+import ctypes as C
+
+import numpy as np
+import torch
+import zmq
+
+from . import native as N
+from .dataset import FileDataset, RemoteIterableDataset, open_pull_socket
+from .file import FileRecorder
+from .preprocess import Preprocess, preprocess_images
+from .staging import Ring, Schema
+
+_DONE = object()
+
+
+def shard(seq, rank, world_size):
+    """Round-robin shard of publishers / recording files for GPU `rank` of `world_size`: the
+    reference's worker model (btt/dataset.py:77-85,97) with GPU = worker; no collective."""
+    return list(seq)[rank::world_size]
+
+
+def _torch_dtype(np_dtype):
+    return torch.from_numpy(np.empty(0, dtype=np_dtype)).dtype
+
+
+class _Stager:
+    """One pinned ring + one CUDA stream; turns filled slots into device batches."""
+
+    def __init__(self, schema, device, depth, specs, keep_raw):
+        self.schema = schema
+        self.device = device
+        self.ring = Ring(schema.slot_bytes, depth, device.index)
+        self.stream = torch.cuda.Stream(device)
+        self.specs = specs
+        self.keep_raw = keep_raw
+        self._scratch = None
+        self.kernels = 0
+
+    def begin(self):
+        return self.ring.acquire()
+
+    def ingest(self, slot, item, msg, host_rows):
+        self.schema.ingest(self.ring.ptr(slot), self.ring.view(slot), item, msg, host_rows)
+
+    def finish(self, slot, n, host_rows):
+        sch = self.schema
+        used = 0
+        for c in sch.columns:
+            used = max(used, c.slot_off + n * c.item_bytes)
+        batch = {}
+        with torch.cuda.stream(self.stream):
+            raw = torch.empty(max(used, 1), dtype=torch.uint8, device=self.device)
+            if used:
+                self.ring.submit(slot, raw.data_ptr(), used, C.c_void_p(self.stream.cuda_stream))
+            for c in sch.columns:
+                t = raw[c.slot_off:c.slot_off + n * c.item_bytes].view(_torch_dtype(c.dtype)).view((n,) + c.shape)
+                spec = self.specs.get(c.key)
+                if spec is not None:
+                    if self._scratch is None and spec.stats:
+                        self._scratch = torch.empty(1 << 17, dtype=torch.uint8, device=self.device)
+                    res = preprocess_images(t, spec, stream=self.stream, _scratch=self._scratch)
+                    self.kernels += 1
+                    if spec.stats:
+                        res, batch[c.key + "_stats"] = res
+                    if self.keep_raw:
+                        batch[c.key + "_raw"] = t
+                    t = res
+                batch[c.key] = t
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        for k in sch.host_keys:
+            batch[k] = host_rows.get(k, [])
+        return batch, ev
+
+    def close(self):
+        self.stream.synchronize()
+        self.ring.close()
+        self.schema.close()
+
+
+class DeviceLoader:
+    """Iterate a `RemoteIterableDataset` or `FileDataset` as collated CUDA batches.
+
+    batch_size, shuffle, drop_last: as in ``torch.utils.data.DataLoader`` (shuffle only for
+        `FileDataset`; streams cannot be shuffled, generate.py:71-72).
+    device: CUDA device of this process (one process per GPU; shard publishers/files with `shard`).
+    preprocess: a `Preprocess` or list of them (one per image field) run on the GPU; None leaves
+        the uint8 frames as they are -- exactly default_collate's output, on the device.
+    num_receivers: receiver threads for streams; each owns a PULL socket connected to all
+        addresses and takes ``max_items // num_receivers`` items, like the reference's DataLoader
+        workers (dataset.py:80-85,97).
+    ring_depth: pinned slots per receiver.  prefetch: finished batches queued ahead of the consumer.
+    ingest_threads: host threads `bt_schema_ingest_many` uses per replay batch.
+    seed: shuffle seed (epoch number is added on every new iteration).
+    keep_raw: also return the untouched uint8 frames as ``<key>_raw``.
+    """
+
+    def __init__(self, dataset, batch_size=1, shuffle=False, drop_last=False, device="cuda",
+                 preprocess=None, num_receivers=1, ring_depth=3, prefetch=2, ingest_threads=4,
+                 seed=0, keep_raw=False):
+        self.dataset = dataset
+        self.batch_size = int(batch_size)
+        if self.batch_size < 1:
+            raise ValueError("batch_size must be >= 1")
+        self.shuffle, self.drop_last = shuffle, drop_last
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("DeviceLoader produces CUDA batches; for host iteration wrap the dataset in "
+                               "torch.utils.data.DataLoader exactly as with the reference")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        if preprocess is None:
+            preprocess = []
+        elif isinstance(preprocess, Preprocess):
+            preprocess = [preprocess]
+        self.specs = {p.key: p for p in preprocess}
+        self.num_receivers = max(1, int(num_receivers))
+        self.ring_depth, self.prefetch = int(ring_depth), int(prefetch)
+        self.ingest_threads = int(ingest_threads)
+        self.seed, self.keep_raw = seed, keep_raw
+        self._epoch = 0
+        self.stats = {"batches": 0, "items": 0, "bytes_h2d": 0, "kernels": 0, "compat_items": 0}
+        if isinstance(dataset, RemoteIterableDataset):
+            if shuffle:
+                raise ValueError("iterable datasets do not support shuffle")
+            self._mode = "stream"
+        elif isinstance(dataset, FileDataset):
+            self._mode = "replay"
+        else:
+            raise TypeError("DeviceLoader takes a btt.RemoteIterableDataset or a btt.FileDataset")
+
+    def __len__(self):
+        if self._mode == "replay":
+            n = len(self.dataset)
+        else:
+            n = (self.dataset.max_items // self.num_receivers) * self.num_receivers
+            per = self.dataset.max_items // self.num_receivers
+            full, rem = divmod(per, self.batch_size)
+            return (full + (1 if rem and not self.drop_last else 0)) * self.num_receivers
+        return n // self.batch_size if self.drop_last else -(-n // self.batch_size)
+
+    # ---- producers --------------------------------------------------------------------------
+    def _new_stager(self, first_msg):
+        schema = Schema.from_message(first_msg, self.batch_size)
+        for key in self.specs:
+            c = schema.column(key)  # KeyError: the named image field is not in the messages
+            if c.dtype != np.uint8:
+                raise TypeError("field %r is %s; preprocessing takes uint8 frames" % (key, c.dtype))
+        return _Stager(schema, self.device, self.ring_depth, self.specs, self.keep_raw)
+
+    def _emit(self, out_q, stop, stager, slot, n, host_rows):
+        batch, ev = stager.finish(slot, n, host_rows)
+        self.stats["bytes_h2d"] += sum(c.item_bytes for c in stager.schema.columns) * n
+        while not stop.is_set():
+            try:
+                out_q.put((batch, ev), timeout=0.1)
+                return True
+            except queue.Full:
+                continue
+        return False
+
+    def _stream_producer(self, rid, out_q, stop):
+        ds = self.dataset
+        stager = None
+        ctx = zmq.Context()
+        sock = None
+        rec = None
+        try:
+            torch.cuda.set_device(self.device)
+            sock, poller = open_pull_socket(ctx, ds.addresses, ds.queue_size)
+            if ds.record_path_prefix is not None:
+                rec = FileRecorder(FileRecorder.filename(ds.record_path_prefix, rid), ds.max_items)
+                rec.__enter__()
+            custom = ds.has_custom_item()
+            slot, filled, host_rows = None, 0, {}
+            for _ in range(ds.max_items // self.num_receivers):
+                if stop.is_set():
+                    return
+                waited = 0
+                while True:  # poll in slices so that an abandoned iterator stops promptly
+                    step = min(100, max(ds.timeoutms - waited, 0))
+                    if sock in dict(poller.poll(step)):
+                        break
+                    waited += step
+                    if stop.is_set():
+                        return
+                    assert waited < ds.timeoutms, "No response within timeout interval."
+                frame = sock.recv(copy=False)
+                msg = frame.buffer
+                if rec is not None:
+                    rec.save(msg, is_pickled=True)
+                if custom:
+                    import pickle
+                    obj = ds._item(pickle.loads(msg))
+                    if stager is None:
+                        stager = _Stager(Schema.from_object(obj, self.batch_size), self.device,
+                                         self.ring_depth, self.specs, self.keep_raw)
+                    if slot is None:
+                        slot, filled, host_rows = stager.begin(), 0, {}
+                    stager.schema.ingest_object(stager.ring.view(slot), filled, obj, host_rows)
+                    self.stats["compat_items"] += 1
+                else:
+                    if stager is None:
+                        stager = self._new_stager(msg)
+                    if slot is None:
+                        slot, filled, host_rows = stager.begin(), 0, {}
+                    stager.ingest(slot, filled, msg, host_rows)
+                filled += 1
+                if filled == self.batch_size:
+                    if not self._emit(out_q, stop, stager, slot, filled, host_rows):
+                        return
+                    slot = None
+            if slot is not None and filled and not self.drop_last:
+                self._emit(out_q, stop, stager, slot, filled, host_rows)
+        except BaseException as e:  # delivered to the consumer thread
+            out_q.put(e)
+        finally:
+            if rec is not None:
+                rec.__exit__(None, None, None)
+            if sock is not None:
+                sock.close()
+            ctx.term()
+            if stager is not None:
+                self.stats["kernels"] += stager.kernels
+                stager.close()
+            out_q.put(_DONE)
+
+    def _replay_order(self):
+        n = len(self.dataset)
+        if self.shuffle:
+            g = torch.Generator()
+            g.manual_seed(self.seed + self._epoch)
+            return torch.randperm(n, generator=g).numpy()
+        return np.arange(n)
+
+    def _replay_producer(self, rid, out_q, stop):
+        ds = self.dataset
+        stager = None
+        try:
+            torch.cuda.set_device(self.device)
+            order = self._replay_order()
+            cum = np.asarray(ds.cumulative_sizes)
+            readers = [d.reader for d in ds.datasets]
+            custom = ds.has_custom_item()
+            B = self.batch_size
+            for start in range(0, len(order), B):
+                if stop.is_set():
+                    return
+                idx = order[start:start + B]
+                if len(idx) < B and self.drop_last:
+                    break
+                fidx = np.searchsorted(cum, idx, side="right")
+                local = idx - np.where(fidx > 0, cum[np.maximum(fidx - 1, 0)], 0)
+                if custom:
+                    objs = [ds._item(readers[f][int(l)]) for f, l in zip(fidx, local)]
+                    if stager is None:
+                        stager = _Stager(Schema.from_object(objs[0], B), self.device, self.ring_depth,
+                                         self.specs, self.keep_raw)
+                    slot, host_rows = stager.begin(), {}
+                    for i, o in enumerate(objs):
+                        stager.schema.ingest_object(stager.ring.view(slot), i, o, host_rows)
+                    self.stats["compat_items"] += len(objs)
+                else:
+                    addrs = np.empty(len(idx), dtype=np.uint64)
+                    lens = np.empty(len(idx), dtype=np.uint64)
+                    for f in np.unique(fidx):
+                        m = fidx == f
+                        addrs[m], lens[m] = readers[f].spans(local[m])
+                    if stager is None:
+                        stager = self._new_stager(readers[fidx[0]].raw(int(local[0])))
+                    slot, host_rows = stager.begin(), {}
+                    done = 0
+                    if stager.schema.native:
+                        bad = stager.schema.ingest_many(stager.ring.ptr(slot), 0, addrs, lens, self.ingest_threads)
+                        done = len(idx) if bad < 0 else -1
+                    if done != len(idx):  # at least one message needs the compatibility decode
+                        for i, (f, l) in enumerate(zip(fidx, local)):
+                            stager.ingest(slot, i, readers[f].raw(int(l)), host_rows)
+                if not self._emit(out_q, stop, stager, slot, len(idx), host_rows):
+                    return
+        except BaseException as e:
+            out_q.put(e)
+        finally:
+            if stager is not None:
+                self.stats["kernels"] += stager.kernels
+                stager.close()
+            out_q.put(_DONE)
+
+    # ---- consumer ---------------------------------------------------------------------------
+    def __iter__(self):
+        out_q = queue.Queue(maxsize=max(1, self.prefetch))
+        stop = threading.Event()
+        if self._mode == "stream":
+            n_prod, target = self.num_receivers, self._stream_producer
+        else:
+            n_prod, target = 1, self._replay_producer
+        threads = [threading.Thread(target=target, args=(r, out_q, stop), daemon=True, name="bt-recv-%d" % r)
+                   for r in range(n_prod)]
+        self._epoch += 1
+        for t in threads:
+            t.start()
+        live = n_prod
+        try:
+            while live:
+                item = out_q.get()
+                if item is _DONE:
+                    live -= 1
+                    continue
+                if isinstance(item, BaseException):
+                    raise item
+                batch, ev = item
+                cur = torch.cuda.current_stream(self.device)
+                cur.wait_event(ev)
+                for v in batch.values():
+                    if isinstance(v, torch.Tensor):
+                        v.record_stream(cur)
+                self.stats["batches"] += 1
+                self.stats["items"] += next((len(v) for v in batch.values()), 0)
+                yield batch
+        finally:
+            stop.set()
+            # unblock producers waiting on a full queue, then let them finish cleanly
+            for t in threads:
+                while t.is_alive():
+                    try:
+                        out_q.get_nowait()
+                    except queue.Empty:
+                        pass
+                    t.join(timeout=0.05)

@@ -1,0 +1,138 @@
+"""Device-side frame preprocessing: the host face of kernel K1.
+
+What users of the reference write as a numpy ``item_transform`` --
+gamma (examples/datagen/generate.py:10-14 == btb/offscreen.py:105-112), normalise + HWC->CHW
+(examples/densityopt/densityopt.py:117-119), flip (btb/offscreen.py:95-96) -- is described
+here declaratively by `Preprocess` and executed for a whole batch by one launch of
+``bt_preprocess_launch`` on the GPU.  There is no CPU implementation in this package.
+"""
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Optional, Sequence, Union
+
+import torch
+
+from . import native as N
+
+_TORCH_OUT = {torch.uint8: N.BT_U8, torch.float32: N.BT_F32, torch.bfloat16: N.BT_BF16}
+VARIANTS = {"auto": 0, "generic": 1, "vector": 2, "bulk": 3}
+
+
+def _per_channel(v, default):
+    if v is None:
+        return [default] * 4
+    if isinstance(v, (int, float)):
+        return [float(v)] * 4
+    v = [float(x) for x in v]
+    if not 1 <= len(v) <= 4:
+        raise ValueError("per-channel values must have 1..4 entries")
+    return v + [default] * (4 - len(v))
+
+
+@dataclass
+class Preprocess:
+    """What to do with the uint8 frames of one message field.
+
+    key:        dict key of the image field (``'image'`` in the reference's examples).
+    flip:       vertical flip (``np.flipud``): for frames sent bottom-up (origin='lower-left').
+    gamma:      gamma coefficient, e.g. 2.2; applied to the first three channels only and
+                truncated to uint8 exactly like the reference; None = off.
+    mean, std:  per-channel (or scalar) normalisation ``(x - mean) / std`` in float32;
+                both None = off (plain cast).
+    layout:     'NCHW' (the reference's ``np.transpose(x, (2, 0, 1))``) or 'NHWC'.
+    dtype:      torch.float32, torch.bfloat16 or torch.uint8 (flip/gamma only).
+    out_channels: keep only the first k channels (e.g. 3 drops alpha); None = all.
+    stats:      also return per-channel [sum, sum of squares] of the batch (float64).
+    """
+    key: str = "image"
+    flip: bool = False
+    gamma: Optional[float] = None
+    mean: Union[None, float, Sequence[float]] = None
+    std: Union[None, float, Sequence[float]] = None
+    layout: str = "NCHW"
+    dtype: torch.dtype = torch.float32
+    out_channels: Optional[int] = None
+    stats: bool = False
+    variant: str = "auto"
+    _lut: bytes = field(default=b"", repr=False)
+
+    def __post_init__(self):
+        if self.layout not in ("NCHW", "NHWC"):
+            raise ValueError("layout must be 'NCHW' or 'NHWC'")
+        if self.dtype not in _TORCH_OUT:
+            raise ValueError("dtype must be torch.float32, torch.bfloat16 or torch.uint8")
+        if self.dtype == torch.uint8 and (self.mean is not None or self.std is not None):
+            raise ValueError("normalisation needs a floating output dtype")
+        if self.variant not in VARIANTS:
+            raise ValueError("variant must be one of %s" % sorted(VARIANTS))
+        if self.gamma:
+            self._lut = N.gamma_lut(self.gamma)
+
+
+def _stream_handle(stream):
+    if stream is None:
+        stream = torch.cuda.current_stream()
+    return C.c_void_p(stream.cuda_stream)
+
+
+def preprocess_images(src, spec, out=None, stream=None, stats_out=None, _scratch=None):
+    """Run K1 on `src`, a CUDA uint8 tensor (B,H,W,C) or (B,H,W), per `spec`.
+
+    Returns the output tensor, or (output, stats) when ``spec.stats``; stats is a
+    (C_out, 2) float64 CUDA tensor [sum, sum of squares].  Work is enqueued on `stream`
+    (default: torch's current stream); nothing is synchronised.
+    """
+    if not src.is_cuda:
+        raise RuntimeError("preprocess_images needs a CUDA tensor; this package has no CPU kernels")
+    if src.dtype != torch.uint8:
+        raise TypeError("frames must be uint8, got %s" % src.dtype)
+    if src.dim() == 3:
+        src = src.unsqueeze(-1)
+    if src.dim() != 4:
+        raise ValueError("expected (B,H,W,C) frames")
+    B, H, W, Cn = src.shape
+    if not 1 <= Cn <= 4:
+        raise ValueError("channels must be 1..4")
+    if src.stride(3) != 1 or src.stride(2) != Cn or src.stride(1) != W * Cn:
+        src = src.contiguous()
+    cout = spec.out_channels or Cn
+    if not 1 <= cout <= Cn:
+        raise ValueError("out_channels must be within 1..channels")
+    shape = (B, cout, H, W) if spec.layout == "NCHW" else (B, H, W, cout)
+    if out is None:
+        out = torch.empty(shape, dtype=spec.dtype, device=src.device)
+    else:
+        if tuple(out.shape) != shape or out.dtype != spec.dtype or not out.is_contiguous():
+            raise ValueError("out must be a contiguous %s tensor of shape %s" % (spec.dtype, shape))
+
+    p = N.PreprocessParams()
+    p.src = src.data_ptr()
+    p.dst = out.data_ptr()
+    p.batch, p.height, p.width, p.channels = B, H, W, Cn
+    p.out_channels = cout
+    p.out_dtype = _TORCH_OUT[spec.dtype]
+    p.flip = int(bool(spec.flip))
+    p.chw = int(spec.layout == "NCHW")
+    p.use_gamma = int(bool(spec.gamma))
+    p.use_norm = int(spec.mean is not None or spec.std is not None)
+    p.variant = VARIANTS[spec.variant]
+    p.src_image_stride = src.stride(0) if B > 1 else 0
+    mean, std = _per_channel(spec.mean, 0.0), _per_channel(spec.std, 1.0)
+    for c in range(4):
+        p.mean[c], p.stdev[c] = mean[c], std[c]
+    if spec.gamma:
+        C.memmove(p.gamma_lut, spec._lut, 256)
+    stats = None
+    if spec.stats:
+        stats = stats_out if stats_out is not None else torch.empty((cout, 2), dtype=torch.float64, device=src.device)
+        p.stats_out = stats.data_ptr()
+        nbytes = N.lib.bt_preprocess_scratch_bytes(C.byref(p))
+        scratch = _scratch
+        if scratch is None or scratch.numel() < nbytes:
+            scratch = torch.empty(nbytes, dtype=torch.uint8, device=src.device)
+        p.stats_scratch = scratch.data_ptr()
+        if stream is not None:
+            scratch.record_stream(stream)
+    with torch.cuda.device(src.device):
+        N.check(N.lib.bt_preprocess_launch(C.byref(p), _stream_handle(stream)))
+    return (out, stats) if spec.stats else out

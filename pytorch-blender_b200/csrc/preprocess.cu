@@ -1,0 +1,468 @@
+// K1: fused uint8 frame preprocessing for sm_100a (B200).
+//
+// One launch per batch does what the reference spreads over numpy and torch on the CPU
+// (see include/bt_b200.h for the cited lines): vertical flip, truncating gamma on RGB, float
+// conversion, (x-mean)/std with IEEE fp32 subtract and divide, HWC->CHW, and the stack into a
+// batch.  The kernel is a pure HBM stream (no reuse): 1 byte read and sizeof(T) bytes written per
+// channel value, so everything here is about wide coalesced accesses, enough bytes in flight and
+// as few instructions per byte as possible.
+//
+// Because the input is uint8, every output value is one of 256 per channel.  Each CTA first
+// builds that table in shared memory *with the reference's own expression* (gamma table entry,
+// then __fsub_rn/__fdiv_rn, then the output cast), so the per-pixel work is one shared-memory
+// lookup per byte and the results are exact by construction -- no FMA contraction, no reciprocal
+// multiply (which is 1.5e-5 relative off).
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstring>
+
+#include "common.h"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxC = 4;
+
+struct K1Args {
+  const uint8_t* src;
+  void* dst;
+  uint32_t B, H, W, C, Cout;
+  uint32_t flip, use_gamma, use_norm;
+  uint64_t src_image_stride;  // bytes
+  float mean[4];
+  float stdev[4];
+  uint8_t gamma_lut[256];
+  double* partials;       // [gridDim.x][kMaxC][2] when stats are on
+  unsigned int* ticket;   // arrival counter, zero on entry, reset to zero on exit
+  double* stats_out;      // [Cout][2]
+};
+
+// ---- output-type helpers -----------------------------------------------------------------
+template <typename T> struct OutT;
+template <> struct OutT<float> {
+  static __device__ __forceinline__ float make(float o, uint8_t) { return o; }
+  static __device__ __forceinline__ float as_float(float v) { return v; }
+};
+template <> struct OutT<__nv_bfloat16> {
+  static __device__ __forceinline__ __nv_bfloat16 make(float o, uint8_t) { return __float2bfloat16_rn(o); }
+  static __device__ __forceinline__ float as_float(__nv_bfloat16 v) { return __bfloat162float(v); }
+};
+template <> struct OutT<uint8_t> {
+  static __device__ __forceinline__ uint8_t make(float, uint8_t g) { return g; }
+  static __device__ __forceinline__ float as_float(uint8_t v) { return (float)v; }
+};
+
+// Build the per-channel value table with the reference's expression.
+template <typename T>
+__device__ __forceinline__ void build_lut(const K1Args& a, T* lut /* [kMaxC][256] */) {
+  for (uint32_t i = threadIdx.x; i < kMaxC * 256; i += blockDim.x) {
+    uint32_t c = i >> 8, v = i & 255;
+    uint8_t g = (a.use_gamma && c < 3) ? a.gamma_lut[v] : (uint8_t)v;
+    float o = (float)g;
+    if (a.use_norm) o = __fdiv_rn(__fsub_rn(o, a.mean[c]), a.stdev[c]);
+    lut[i] = OutT<T>::make(o, g);
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+// Store N consecutive T (N*sizeof(T) in {4, 8, 16, 32, 64}) with streaming (evict-first) hints.
+template <typename T, int N>
+__device__ __forceinline__ void st_stream(T* dst, const T (&v)[N]) {
+  constexpr int bytes = N * (int)sizeof(T);
+  static_assert(bytes == 4 || bytes == 8 || bytes % 16 == 0, "unsupported store width");
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(v);
+  if constexpr (bytes == 4) {
+    __stcs(reinterpret_cast<unsigned int*>(dst), w[0]);
+  } else if constexpr (bytes == 8) {
+    __stcs(reinterpret_cast<uint2*>(dst), make_uint2(w[0], w[1]));
+  } else {
+#pragma unroll
+    for (int k = 0; k < bytes / 16; ++k)
+      __stcs(reinterpret_cast<uint4*>(dst) + k, make_uint4(w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]));
+  }
+}
+
+__device__ __forceinline__ uint32_t byte_of(const uint32_t* words, int k) {
+  return (words[k >> 2] >> (8 * (k & 3))) & 0xffu;
+}
+
+// ---- deterministic per-batch statistics ----------------------------------------------------
+struct StatAcc {
+  double s[kMaxC], q[kMaxC];
+  __device__ __forceinline__ void clear() {
+#pragma unroll
+    for (int c = 0; c < kMaxC; ++c) s[c] = q[c] = 0.0;
+  }
+};
+
+__device__ __forceinline__ double shfl_down_f64(double v, int d) {
+  int lo = __double2loint(v), hi = __double2hiint(v);
+  lo = __shfl_down_sync(0xffffffffu, lo, d);
+  hi = __shfl_down_sync(0xffffffffu, hi, d);
+  return __hiloint2double(hi, lo);
+}
+
+// warp shuffle -> shared -> one partial row per CTA -> last CTA folds the rows in index order.
+__device__ void finish_stats(const K1Args& a, StatAcc& acc) {
+  __shared__ double red[kThreads / 32][kMaxC][2];
+  __shared__ bool last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int c = 0; c < kMaxC; ++c) {
+    double s = acc.s[c], q = acc.q[c];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      s += shfl_down_f64(s, d);
+      q += shfl_down_f64(q, d);
+    }
+    if (lane == 0) { red[warp][c][0] = s; red[warp][c][1] = q; }
+  }
+  __syncthreads();
+  if (threadIdx.x < kMaxC * 2) {
+    int c = threadIdx.x >> 1, k = threadIdx.x & 1;
+    double t = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w][c][k];
+    a.partials[((size_t)blockIdx.x * kMaxC + c) * 2 + k] = t;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(a.ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  if (threadIdx.x < a.Cout * 2) {
+    int c = threadIdx.x >> 1, k = threadIdx.x & 1;
+    double t = 0.0;
+    for (unsigned b = 0; b < gridDim.x; ++b) t += __ldcg(&a.partials[((size_t)b * kMaxC + c) * 2 + k]);
+    a.stats_out[c * 2 + k] = t;
+  }
+  if (threadIdx.x == 0) *a.ticket = 0;  // ready for the next launch
+}
+
+// ---- variant 1: generic scalar (any shape) -----------------------------------------------
+template <typename T, bool CHW, bool STATS>
+__global__ void __launch_bounds__(kThreads) k1_generic(K1Args a) {
+  __shared__ T lut[kMaxC * 256];
+  build_lut<T>(a, lut);
+  StatAcc acc;
+  if (STATS) acc.clear();
+  const uint64_t per_image = (uint64_t)a.H * a.W * a.Cout;
+  const uint64_t total = per_image * a.B;
+  T* dst = static_cast<T*>(a.dst);
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (uint64_t)gridDim.x * blockDim.x) {
+    uint32_t b = (uint32_t)(i / per_image);
+    uint32_t r = (uint32_t)(i - (uint64_t)b * per_image);
+    uint32_t c, y, x;
+    if (CHW) { c = r / (a.H * a.W); uint32_t p = r - c * a.H * a.W; y = p / a.W; x = p - y * a.W; }
+    else { uint32_t p = r / a.Cout; c = r - p * a.Cout; y = p / a.W; x = p - y * a.W; }
+    uint32_t sy = a.flip ? a.H - 1 - y : y;
+    uint8_t v = a.src[(uint64_t)b * a.src_image_stride + ((uint64_t)sy * a.W + x) * a.C + c];
+    T o = lut[c * 256 + v];
+    dst[i] = o;
+    if (STATS) {
+      float f = OutT<T>::as_float(o);
+#pragma unroll
+      for (int cc = 0; cc < kMaxC; ++cc)
+        if (cc == (int)c) { acc.s[cc] += f; acc.q[cc] += (double)f * f; }
+    }
+  }
+  if (STATS) finish_stats(a, acc);
+}
+
+// ---- variant 2: register-vectorised, planar (CHW) output ---------------------------------------
+// One "unit" is PPT consecutive pixels of one row: PPT*C bytes in (16-byte loads), PPT values out
+// per plane (16-byte stores where PPT*sizeof(T) allows).  A warp therefore reads 32*PPT*C
+// contiguous bytes and writes 32*PPT*sizeof(T) contiguous bytes per plane.  UNROLL units per
+// thread are loaded before any is consumed, to keep >= UNROLL*PPT*C bytes in flight per thread.
+template <typename T, int C, int PPT, int UNROLL, bool STATS>
+__global__ void __launch_bounds__(kThreads) k1_planar(K1Args a) {
+  static_assert((PPT * C) % 16 == 0, "unit must be whole 16-byte loads");
+  constexpr int LOADS = PPT * C / 16;
+  __shared__ T lut[kMaxC * 256];
+  build_lut<T>(a, lut);
+  StatAcc acc;
+  if (STATS) acc.clear();
+
+  const uint32_t upr = a.W / PPT;                     // units per row
+  const uint64_t rows = (uint64_t)a.B * a.H;
+  const uint64_t total = rows * upr;
+  const uint64_t plane = (uint64_t)a.H * a.W;
+  T* dst = static_cast<T*>(a.dst);
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+
+  for (uint64_t u0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; u0 < total; u0 += stride * UNROLL) {
+    uint4 in[UNROLL][LOADS];
+    uint64_t out_off[UNROLL];
+    bool live[UNROLL];
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      uint64_t u = u0 + (uint64_t)j * stride;
+      live[j] = u < total;
+      if (live[j]) {
+        uint64_t row = u / upr;
+        uint32_t ux = (uint32_t)(u - row * upr);
+        uint32_t b = (uint32_t)(row / a.H);
+        uint32_t y = (uint32_t)(row - (uint64_t)b * a.H);
+        uint32_t sy = a.flip ? a.H - 1 - y : y;
+        const uint4* sp = reinterpret_cast<const uint4*>(
+            a.src + (uint64_t)b * a.src_image_stride + ((uint64_t)sy * a.W + (uint64_t)ux * PPT) * C);
+#pragma unroll
+        for (int l = 0; l < LOADS; ++l) in[j][l] = ld_stream(sp + l);
+        out_off[j] = (uint64_t)b * a.Cout * plane + (uint64_t)y * a.W + (uint64_t)ux * PPT;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      if (!live[j]) continue;
+      const uint32_t* words = reinterpret_cast<const uint32_t*>(&in[j][0]);
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        if (c < (int)a.Cout) {
+          T vals[PPT];
+          float fs = 0.f, fq = 0.f;
+#pragma unroll
+          for (int p = 0; p < PPT; ++p) {
+            vals[p] = lut[c * 256 + byte_of(words, p * C + c)];
+            if (STATS) { float f = OutT<T>::as_float(vals[p]); fs += f; fq = fmaf(f, f, fq); }
+          }
+          st_stream<T, PPT>(dst + out_off[j] + (uint64_t)c * plane, vals);
+          if (STATS) { acc.s[c] += (double)fs; acc.q[c] += (double)fq; }
+        }
+      }
+    }
+  }
+  if (STATS) finish_stats(a, acc);
+}
+
+// ---- variant 2b: register-vectorised, interleaved (HWC) output ---------------------------------
+// Rows are streams of W*C bytes; a unit is 16 bytes of one row.  Needs Cout == C.
+template <typename T, int UNROLL, bool STATS>
+__global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a) {
+  __shared__ T lut[kMaxC * 256];
+  build_lut<T>(a, lut);
+  StatAcc acc;
+  if (STATS) acc.clear();
+  const uint32_t row_bytes = a.W * a.C;
+  const uint32_t upr = row_bytes / 16;
+  const uint64_t rows = (uint64_t)a.B * a.H;
+  const uint64_t total = rows * upr;
+  T* dst = static_cast<T*>(a.dst);
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint32_t C = a.C;
+
+  for (uint64_t u0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; u0 < total; u0 += stride * UNROLL) {
+    uint4 in[UNROLL];
+    uint64_t out_off[UNROLL];
+    uint32_t phase[UNROLL];
+    bool live[UNROLL];
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      uint64_t u = u0 + (uint64_t)j * stride;
+      live[j] = u < total;
+      if (live[j]) {
+        uint64_t row = u / upr;
+        uint32_t ux = (uint32_t)(u - row * upr);
+        uint32_t b = (uint32_t)(row / a.H);
+        uint32_t y = (uint32_t)(row - (uint64_t)b * a.H);
+        uint32_t sy = a.flip ? a.H - 1 - y : y;
+        in[j] = ld_stream(reinterpret_cast<const uint4*>(
+            a.src + (uint64_t)b * a.src_image_stride + (uint64_t)sy * row_bytes + (uint64_t)ux * 16));
+        out_off[j] = row * row_bytes + (uint64_t)ux * 16;
+        phase[j] = (ux * 16u) % C;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      if (!live[j]) continue;
+      const uint32_t* words = reinterpret_cast<const uint32_t*>(&in[j]);
+      T vals[16];
+      uint32_t c = phase[j];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        vals[k] = lut[c * 256 + byte_of(words, k)];
+        if (STATS) {
+          float f = OutT<T>::as_float(vals[k]);
+#pragma unroll
+          for (int cc = 0; cc < kMaxC; ++cc)
+            if (cc == (int)c) { acc.s[cc] += f; acc.q[cc] += (double)f * f; }
+        }
+        c = (c + 1 == C) ? 0 : c + 1;
+      }
+      st_stream<T, 16>(dst + out_off[j], vals);
+    }
+  }
+  if (STATS) finish_stats(a, acc);
+}
+
+thread_local int g_last_variant = 0;
+
+int grid_for(uint64_t units_per_thread_total, int device_sms, int ctas_per_sm) {
+  uint64_t need = (units_per_thread_total + kThreads - 1) / kThreads;
+  uint64_t cap = (uint64_t)device_sms * ctas_per_sm;
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
+}
+
+int sm_count() {
+  static thread_local int cached_dev = -1, cached = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev != cached_dev) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached = n;
+    cached_dev = dev;
+  }
+  return cached;
+}
+
+template <typename T, bool STATS>
+int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStream_t st, int grid_cap) {
+  const int sms = sm_count();
+  const uint64_t rows = (uint64_t)a.B * a.H;
+  const bool aligned_src = (reinterpret_cast<uintptr_t>(a.src) % 16 == 0) && (a.src_image_stride % 16 == 0);
+  const bool aligned_dst = reinterpret_cast<uintptr_t>(a.dst) % 16 == 0;
+  const bool can_vec = aligned_src && aligned_dst && variant != 1;
+  auto grid_of = [&](uint64_t units, int unroll) {
+    int g = grid_for((units + unroll - 1) / unroll, sms, 8);
+    if (grid_cap > 0 && g > grid_cap) g = grid_cap;
+    return g;
+  };
+#define LAUNCH_PLANAR(C_, PPT_, UNR_)                                                       \
+  do {                                                                                      \
+    int g = grid_of(rows * (a.W / (PPT_)), (UNR_));                                         \
+    k1_planar<T, C_, PPT_, UNR_, STATS><<<g, kThreads, 0, st>>>(a);                         \
+    g_last_variant = 2;                                                                     \
+    return g;                                                                               \
+  } while (0)
+  if (can_vec && p->chw && a.C == 4) {
+    // widest unit whose stores are 16 bytes and that divides the row
+    if (sizeof(T) == 1 && a.W % 16 == 0) LAUNCH_PLANAR(4, 16, 2);
+    if (sizeof(T) == 2 && a.W % 8 == 0) LAUNCH_PLANAR(4, 8, 2);
+    if (a.W % 4 == 0) LAUNCH_PLANAR(4, 4, 4);
+  }
+  if (can_vec && p->chw && a.C == 3 && a.W % 16 == 0) LAUNCH_PLANAR(3, 16, 2);
+#undef LAUNCH_PLANAR
+  if (can_vec && (!p->chw || a.C == 1) && a.Cout == a.C && (a.W * a.C) % 16 == 0 &&
+      (16 * sizeof(T)) % 16 == 0) {
+    int g = grid_of(rows * (a.W * a.C / 16), 4);
+    k1_interleaved<T, 4, STATS><<<g, kThreads, 0, st>>>(a);
+    g_last_variant = 2;
+    return g;
+  }
+  if (variant == 2 || variant == 3)
+    return bt::fail(BT_E_INVALID, "requested vectorised variant needs 16-byte aligned rows (W=%u C=%u)", a.W, a.C);
+  {
+    uint64_t total = rows * a.W * a.Cout;
+    int g = grid_of(total, 1);
+    if (p->chw) k1_generic<T, true, STATS><<<g, kThreads, 0, st>>>(a);
+    else k1_generic<T, false, STATS><<<g, kThreads, 0, st>>>(a);
+    g_last_variant = 1;
+    return g;
+  }
+}
+
+constexpr int kStatsMaxGrid = 148 * 8;
+
+}  // namespace
+
+extern "C" {
+
+int bt_build_gamma_lut(double coeff, uint8_t lut[256]) {
+  if (!lut || !(coeff > 0.0)) return bt::fail(BT_E_INVALID, "gamma coefficient must be positive");
+  // offscreen.py:106-108 in float32: x.astype(f32)/255, ** (1/coeff) with the exponent rounded to
+  // float32 (numpy weak-scalar promotion), times 255.0 in float32, truncating uint8 cast.
+  const float e = (float)(1.0 / coeff);
+  for (int v = 0; v < 256; ++v) {
+    float x = (float)v / 255.0f;
+    float y = 255.0f * powf(x, e);
+    lut[v] = (uint8_t)y;
+  }
+  return BT_OK;
+}
+
+uint64_t bt_preprocess_scratch_bytes(const bt_preprocess_params* p) {
+  if (!p || !p->stats_out) return 0;
+  return (uint64_t)kStatsMaxGrid * kMaxC * 2 * sizeof(double) + 256;
+}
+
+int bt_preprocess_last_variant(void) { return g_last_variant; }
+
+int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) {
+  if (!p || !p->src || !p->dst) return bt::fail(BT_E_INVALID, "bt_preprocess_launch: null pointer");
+  if (p->batch < 0 || p->height < 0 || p->width < 0) return bt::fail(BT_E_INVALID, "negative extent");
+  if (p->channels < 1 || p->channels > kMaxC) return bt::fail(BT_E_INVALID, "channels must be 1..4, got %d", p->channels);
+  if (p->out_channels < 1 || p->out_channels > p->channels)
+    return bt::fail(BT_E_INVALID, "out_channels must be 1..channels, got %d", p->out_channels);
+  if (p->out_dtype != BT_U8 && p->out_dtype != BT_F32 && p->out_dtype != BT_BF16)
+    return bt::fail(BT_E_INVALID, "out_dtype must be u8, f32 or bf16");
+  if (p->stats_out && !p->stats_scratch) return bt::fail(BT_E_INVALID, "stats_out needs stats_scratch");
+  if ((uint64_t)p->height * p->width * p->channels >= (1ull << 32))
+    return bt::fail(BT_E_INVALID, "single frames of 4 GiB or more are not supported");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+  K1Args a;
+  memset(&a, 0, sizeof a);
+  a.src = static_cast<const uint8_t*>(p->src);
+  a.dst = p->dst;
+  a.B = p->batch; a.H = p->height; a.W = p->width; a.C = p->channels; a.Cout = p->out_channels;
+  a.flip = p->flip != 0;
+  a.use_gamma = p->use_gamma != 0;
+  a.use_norm = (p->use_norm != 0) && p->out_dtype != BT_U8;
+  const uint64_t dense = (uint64_t)p->height * p->width * p->channels;
+  a.src_image_stride = p->src_image_stride ? p->src_image_stride : dense;
+  if (a.src_image_stride < dense) return bt::fail(BT_E_INVALID, "src_image_stride smaller than one frame");
+  memcpy(a.mean, p->mean, sizeof a.mean);
+  memcpy(a.stdev, p->stdev, sizeof a.stdev);
+  memcpy(a.gamma_lut, p->gamma_lut, 256);
+  if (a.use_norm)
+    for (int c = 0; c < p->channels; ++c)
+      if (a.stdev[c] == 0.0f) return bt::fail(BT_E_INVALID, "stdev[%d] is zero", c);
+
+  const bool stats = p->stats_out != nullptr;
+  if (stats) {
+    a.partials = static_cast<double*>(p->stats_scratch);
+    a.ticket = reinterpret_cast<unsigned int*>(static_cast<uint8_t*>(p->stats_scratch) +
+                                               (uint64_t)kStatsMaxGrid * kMaxC * 2 * sizeof(double));
+    a.stats_out = p->stats_out;
+  }
+  if ((uint64_t)a.B * a.H * a.W == 0) {
+    if (stats) BT_CUDA_TRY(cudaMemsetAsync(p->stats_out, 0, sizeof(double) * 2 * a.Cout, st));
+    g_last_variant = 0;
+    return BT_OK;
+  }
+  if (stats) {
+    // the arrival counter must start at zero; the kernel leaves it at zero, this covers first use
+    BT_CUDA_TRY(cudaMemsetAsync(a.ticket, 0, sizeof(unsigned int), st));
+  }
+
+  int g = 0;
+  const int cap = stats ? kStatsMaxGrid : 0;
+  switch (p->out_dtype) {
+    case BT_F32:
+      g = stats ? launch_typed<float, true>(p, a, p->variant, st, cap) : launch_typed<float, false>(p, a, p->variant, st, cap);
+      break;
+    case BT_BF16:
+      g = stats ? launch_typed<__nv_bfloat16, true>(p, a, p->variant, st, cap)
+                : launch_typed<__nv_bfloat16, false>(p, a, p->variant, st, cap);
+      break;
+    default:
+      g = stats ? launch_typed<uint8_t, true>(p, a, p->variant, st, cap) : launch_typed<uint8_t, false>(p, a, p->variant, st, cap);
+      break;
+  }
+  if (g < 0) return g;
+  BT_CUDA_TRY(cudaGetLastError());
+  return BT_OK;
+}
+
+}  // extern "C"

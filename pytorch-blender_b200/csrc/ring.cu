@@ -1,0 +1,171 @@
+// Pinned, batch-contiguous staging ring + H2D submission.
+//
+// Replaces the reference's host hand-off chain for a batch (DataLoader worker -> shared-memory
+// tensor -> main process -> pageable `.to(dev)`; torch collate.py:269-275 and
+// examples/densityopt/densityopt.py:261,268) with: payload memcpy into a page-locked slot
+// (scan.cpp) -> one cudaMemcpyAsync per batch on the caller's copy stream -> event.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "common.h"
+
+struct bt_ring {
+  int device = -1;
+  uint64_t slot_bytes = 0;
+  int depth = 0;
+  uint8_t* base = nullptr;
+  bool pinned = false;
+  std::vector<cudaEvent_t> done;
+  std::vector<uint8_t> in_flight;
+  int next = 0;
+};
+
+extern "C" {
+
+int bt_ring_create(int device, uint64_t slot_bytes, int depth, bt_ring** out) {
+  if (!out || depth < 1 || slot_bytes == 0) return bt::fail(BT_E_INVALID, "bt_ring_create: bad arguments");
+  bt_ring* r = new (std::nothrow) bt_ring();
+  if (!r) return bt::fail(BT_E_NOMEM, "out of memory");
+  r->device = device;
+  r->slot_bytes = bt::align_up(slot_bytes, 4096);
+  r->depth = depth;
+  r->in_flight.assign(depth, 0);
+  if (device >= 0) {
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess)
+      e = cudaHostAlloc(reinterpret_cast<void**>(&r->base), r->slot_bytes * depth, cudaHostAllocPortable);
+    if (e != cudaSuccess) {
+      delete r;
+      return bt::fail(BT_E_CUDA, "pinned ring allocation (%llu bytes) failed: %s",
+                      (unsigned long long)(slot_bytes * depth), cudaGetErrorString(e));
+    }
+    r->pinned = true;
+    r->done.resize(depth);
+    for (int i = 0; i < depth; ++i) {
+      e = cudaEventCreateWithFlags(&r->done[i], cudaEventDisableTiming);
+      if (e != cudaSuccess) {
+        for (int j = 0; j < i; ++j) cudaEventDestroy(r->done[j]);
+        cudaFreeHost(r->base);
+        delete r;
+        return bt::fail(BT_E_CUDA, "cudaEventCreate failed: %s", cudaGetErrorString(e));
+      }
+    }
+  } else {
+    void* p = nullptr;
+    if (posix_memalign(&p, 4096, r->slot_bytes * depth) != 0) {
+      delete r;
+      return bt::fail(BT_E_NOMEM, "ring allocation failed");
+    }
+    r->base = static_cast<uint8_t*>(p);
+  }
+  // touch every page once so first-use faults are not charged to the ingest loop
+  memset(r->base, 0, r->slot_bytes * depth);
+  *out = r;
+  return BT_OK;
+}
+
+int bt_ring_destroy(bt_ring* r) {
+  if (!r) return BT_OK;
+  if (r->pinned) {
+    for (int i = 0; i < r->depth; ++i) {
+      if (r->in_flight[i]) cudaEventSynchronize(r->done[i]);
+      cudaEventDestroy(r->done[i]);
+    }
+    cudaFreeHost(r->base);
+  } else {
+    free(r->base);
+  }
+  delete r;
+  return BT_OK;
+}
+
+int bt_ring_depth(const bt_ring* r) { return r ? r->depth : bt::fail(BT_E_INVALID, "null ring"); }
+uint64_t bt_ring_slot_bytes(const bt_ring* r) { return r ? r->slot_bytes : 0; }
+
+void* bt_ring_slot_ptr(bt_ring* r, int slot) {
+  if (!r || slot < 0 || slot >= r->depth) {
+    bt::fail(BT_E_INVALID, "bt_ring_slot_ptr: bad slot");
+    return nullptr;
+  }
+  return r->base + r->slot_bytes * (uint64_t)slot;
+}
+
+int bt_ring_wait(bt_ring* r, int slot) {
+  if (!r || slot < 0 || slot >= r->depth) return bt::fail(BT_E_INVALID, "bt_ring_wait: bad slot");
+  if (r->pinned && r->in_flight[slot]) {
+    BT_CUDA_TRY(cudaEventSynchronize(r->done[slot]));
+    r->in_flight[slot] = 0;
+  }
+  return BT_OK;
+}
+
+int bt_ring_acquire(bt_ring* r, int* slot) {
+  if (!r || !slot) return bt::fail(BT_E_INVALID, "bt_ring_acquire: bad arguments");
+  int s = r->next;
+  r->next = (r->next + 1) % r->depth;
+  int rc = bt_ring_wait(r, s);
+  if (rc != BT_OK) return rc;
+  *slot = s;
+  return BT_OK;
+}
+
+int bt_ring_submit(bt_ring* r, int slot, void* dev_dst, uint64_t nbytes, void* stream) {
+  if (!r || slot < 0 || slot >= r->depth || !dev_dst || nbytes > r->slot_bytes)
+    return bt::fail(BT_E_INVALID, "bt_ring_submit: bad arguments");
+  if (!r->pinned) return bt::fail(BT_E_CUDA, "ring was created without a CUDA device; nothing to copy to");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  BT_CUDA_TRY(cudaMemcpyAsync(dev_dst, r->base + r->slot_bytes * (uint64_t)slot, nbytes, cudaMemcpyHostToDevice, st));
+  BT_CUDA_TRY(cudaEventRecord(r->done[slot], st));
+  r->in_flight[slot] = 1;
+  return BT_OK;
+}
+
+int bt_device_count(int* n) {
+  if (!n) return bt::fail(BT_E_INVALID, "null argument");
+  cudaError_t e = cudaGetDeviceCount(n);
+  if (e != cudaSuccess) {
+    *n = 0;
+    return bt::fail(BT_E_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
+  }
+  return BT_OK;
+}
+
+int bt_measure_h2d(int device, uint64_t nbytes, int iters, double* gb_per_s) {
+  if (!gb_per_s || nbytes == 0 || iters < 1) return bt::fail(BT_E_INVALID, "bt_measure_h2d: bad arguments");
+  BT_CUDA_TRY(cudaSetDevice(device));
+  void *h = nullptr, *d = nullptr;
+  cudaStream_t st = nullptr;
+  cudaEvent_t a = nullptr, b = nullptr;
+  int rc = BT_OK;
+  float ms = 0;
+  cudaError_t e;
+#define STEP(x) if ((e = (x)) != cudaSuccess) { rc = bt::fail(BT_E_CUDA, "%s: %s", #x, cudaGetErrorString(e)); goto out; }
+  STEP(cudaHostAlloc(&h, nbytes, cudaHostAllocDefault));
+  memset(h, 1, nbytes);
+  STEP(cudaMalloc(&d, nbytes));
+  STEP(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  STEP(cudaEventCreate(&a));
+  STEP(cudaEventCreate(&b));
+  for (int i = 0; i < 2; ++i) STEP(cudaMemcpyAsync(d, h, nbytes, cudaMemcpyHostToDevice, st));
+  STEP(cudaEventRecord(a, st));
+  for (int i = 0; i < iters; ++i) STEP(cudaMemcpyAsync(d, h, nbytes, cudaMemcpyHostToDevice, st));
+  STEP(cudaEventRecord(b, st));
+  STEP(cudaEventSynchronize(b));
+  STEP(cudaEventElapsedTime(&ms, a, b));
+  *gb_per_s = (double)nbytes * iters / (ms * 1e-3) / 1e9;
+#undef STEP
+out:
+  if (a) cudaEventDestroy(a);
+  if (b) cudaEventDestroy(b);
+  if (st) cudaStreamDestroy(st);
+  if (d) cudaFree(d);
+  if (h) cudaFreeHost(h);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,99 @@
+"""`.btr` writer/reader: byte compatibility with the reference in both directions
+(btt/file.py), the reference's own test protocol (tests/test_file.py:5-13), and the
+zero-unpickle raw/span access."""
+import pickle
+
+import numpy as np
+import pytest
+
+from blendtorch import btt
+from blendtorch.btt.file import FileReader, FileRecorder
+from oracle import btr as obtr
+
+
+def test_file_recorder_reader(tmp_path):
+    # same statements as the reference's tests/test_file.py:5-13
+    with FileRecorder(outpath=tmp_path / "record.mpkl", max_messages=10) as rec:
+        for i in range(7):
+            rec.save({"value": i}, is_pickled=False)
+    r = FileReader(tmp_path / "record.mpkl")
+    assert len(r) == 7
+    for i in range(7):
+        assert r[i]["value"] == i
+    # random access works too (the reference's shared-memo files only replay sequentially)
+    assert [r[i]["value"] for i in (5, 0, 3)] == [5, 0, 3]
+    # and the oracle (= reference algorithm) reads the file we wrote
+    o = obtr.Reader(tmp_path / "record.mpkl")
+    assert [o[i]["value"] for i in range(7)] == list(range(7))
+
+
+def test_reads_reference_written_files(golden_dir):
+    r = FileReader(golden_dir / "file_roundtrip.btr")   # written by the reference with its shared memo
+    assert len(r) == 7
+    assert [r[i]["value"] for i in range(7)] == list(range(7))
+    for pub, n in enumerate((6, 5)):
+        r = FileReader(golden_dir / ("rec_small_%02d.btr" % pub))
+        o = obtr.Reader(golden_dir / ("rec_small_%02d.btr" % pub))
+        assert len(r) == n
+        for i in (n - 1, 0, 2):
+            a, b = r[i], o[i]
+            assert a.keys() == b.keys()
+            np.testing.assert_array_equal(a["image"], b["image"])
+            assert pickle.loads(r.raw(i)).keys() == a.keys()
+            np.testing.assert_array_equal(pickle.loads(r.raw(i))["xy"], b["xy"])
+        r.close()
+
+
+def test_writes_reference_identical_bytes(golden_dir, tmp_path):
+    for pub in range(2):
+        src = FileReader(golden_dir / ("rec_small_%02d.btr" % pub))
+        out = tmp_path / ("copy_%02d.btr" % pub)
+        with FileRecorder(out, max_messages=8) as rec:
+            for i in range(len(src)):
+                rec.save(src.raw(i), is_pickled=True)
+        assert out.read_bytes() == (golden_dir / ("rec_small_%02d.btr" % pub)).read_bytes()
+
+
+def test_capacity_and_errors(tmp_path):
+    with FileRecorder(tmp_path / "cap.btr", max_messages=3) as rec:
+        for i in range(5):
+            rec.save({"v": i})              # beyond capacity: silently dropped (file.py:46)
+    r = FileReader(tmp_path / "cap.btr")
+    assert len(r) == 3 and r[2]["v"] == 2
+    with pytest.raises(AssertionError, match="Cannot open .* for reading"):
+        FileReader(tmp_path / "missing.btr")
+    with pytest.raises(AssertionError, match="Found no recording files with prefix"):
+        btt.FileDataset(str(tmp_path / "nothing"))
+    assert FileRecorder.filename("a/b", 3) == "a/b_03.btr"
+    # empty recording
+    with FileRecorder(tmp_path / "empty.btr", max_messages=4):
+        pass
+    assert len(FileReader(tmp_path / "empty.btr")) == 0
+
+
+def test_filedataset_matches_reference_replay(golden_dir):
+    """FileDataset + torch DataLoader (host iteration) reproduces the reference's collated
+    batches recorded in rec_small_expected.npz."""
+    from torch.utils.data import DataLoader
+    exp = np.load(golden_dir / "rec_small_expected.npz")
+    ds = btt.FileDataset(str(golden_dir / "rec_small"))
+    assert len(ds) == 11
+    for k, b in enumerate(DataLoader(ds, batch_size=4, shuffle=False, num_workers=0)):
+        for key in ("image", "xy", "frameid", "btid"):
+            got = b[key].numpy()
+            assert got.dtype == exp["raw_b%d_%s" % (k, key)].dtype
+            np.testing.assert_array_equal(got, exp["raw_b%d_%s" % (k, key)])
+    # with workers: a fresh dataset per loader (SURVEY defect 4)
+    ds = btt.FileDataset(str(golden_dir / "rec_small"), item_transform=lambda it: {"f": it["frameid"]})
+    got = sorted(int(x) for b in DataLoader(ds, batch_size=4, num_workers=2) for x in b["f"])
+    assert got == sorted(list(range(6)) + list(range(5)))
+
+
+def test_spans_point_at_messages(golden_dir):
+    import ctypes
+    r = FileReader(golden_dir / "rec_small_00.btr")
+    addrs, lens = r.spans([0, 3, 5])
+    for a, l, i in zip(addrs, lens, (0, 3, 5)):
+        blob = ctypes.string_at(int(a), int(l))
+        assert blob == bytes(r.raw(i))
+        assert pickle.loads(blob)["frameid"] == i

@@ -1,0 +1,184 @@
+"""K1 parity: bt_preprocess_launch (through the C ABI) against the oracle and against the
+outputs of the unmodified reference (tests/golden/rec_small_expected.npz).
+
+Bars (BASELINE.json north_star): bit-exact for uint8 work, flips and transposes; float32 within
+1e-6 relative -- here it is in fact bit-exact, which is asserted; bfloat16 within 1 ulp (asserted
+0 ulp against round-to-nearest-even of the float32 oracle)."""
+import itertools
+
+import numpy as np
+import pytest
+import torch
+
+from blendtorch import btt
+from oracle import btr, preprocess as opre
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def _run(frames, **kw):
+    spec = btt.Preprocess(**kw)
+    src = torch.from_numpy(np.ascontiguousarray(frames)).to(DEV)
+    out = btt.preprocess_images(src, spec)
+    if spec.stats:
+        out, st = out
+        torch.cuda.synchronize()
+        return out, st
+    torch.cuda.synchronize()
+    return out
+
+
+def _oracle(frames, flip, gamma, mean, std, layout, dtype, out_channels=None):
+    out_dtype = "uint8" if dtype == torch.uint8 else "float32"
+    exp = opre.preprocess_batch(list(frames), flip=flip, gamma=gamma, mean=mean, std=std,
+                                chw=(layout == "NCHW"), out_dtype=out_dtype)
+    if out_channels:
+        exp = exp[:, :out_channels] if layout == "NCHW" else exp[..., :out_channels]
+    return np.ascontiguousarray(exp)
+
+
+def _assert_matches(out, exp, dtype):
+    if dtype == torch.bfloat16:
+        got = out.view(torch.int16).cpu().numpy().view(np.uint16)
+        want = opre.to_bf16_bits(exp)
+        ulp = np.abs(got.astype(np.int32) - want.astype(np.int32)).max() if got.size else 0
+        assert ulp <= 1, "bf16 differs by %d ulp" % ulp   # tolerance stated by north_star
+        assert ulp == 0
+    else:
+        got = out.cpu().numpy()
+        assert got.dtype == exp.dtype and got.shape == exp.shape
+        if got.dtype == np.float32:
+            # bit-exact, which implies the 1e-6 relative bar
+            np.testing.assert_array_equal(got.view(np.uint32), exp.view(np.uint32))
+        else:
+            np.testing.assert_array_equal(got, exp)
+
+
+SHAPES = [(2, 12, 16, 4), (3, 7, 5, 4), (2, 9, 16, 3), (2, 8, 32, 3), (1, 5, 16, 1), (2, 6, 10, 2),
+          (1, 4, 8, 4), (2, 3, 24, 4), (5, 1, 4, 4), (1, 33, 48, 3)]
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.uint8])
+def test_parity_sweep(shape, dtype):
+    rng = np.random.default_rng(hash(shape) % 2 ** 32)
+    frames = rng.integers(0, 256, shape, dtype=np.uint8)
+    C = shape[3]
+    norms = [(None, None)] if dtype == torch.uint8 else [
+        (None, None), (127.5, 127.5), ([0.485 * 255, 0.456 * 255, 0.406 * 255, 3.0][:C], [58.4, 57.1, 57.4, 2.0][:C])]
+    for flip, gamma, (mean, std), layout in itertools.product((False, True), (None, 2.2), norms, ("NCHW", "NHWC")):
+        out = _run(frames, flip=flip, gamma=gamma, mean=mean, std=std, layout=layout, dtype=dtype)
+        _assert_matches(out, _oracle(frames, flip, gamma, mean, std, layout, dtype), dtype)
+    if C == 4:
+        out = _run(frames, gamma=2.2, mean=127.5, std=127.5, dtype=dtype if dtype != torch.uint8 else torch.float32,
+                   out_channels=3)
+        _assert_matches(out, _oracle(frames, False, 2.2, 127.5, 127.5, "NCHW", torch.float32, 3),
+                        dtype if dtype != torch.uint8 else torch.float32)
+
+
+def test_against_reference_fixture(golden_dir):
+    exp = np.load(golden_dir / "rec_small_expected.npz")
+    ds = btr.ReplayDataset(str(golden_dir / "rec_small"))
+    frames = np.stack([ds[i]["image"] for i in range(len(ds))])
+    want = np.concatenate([exp["gamma_norm_b%d_image" % k] for k in range(3)])
+    got = _run(frames, gamma=2.2, mean=127.5, std=127.5).cpu().numpy()
+    np.testing.assert_array_equal(got.view(np.uint32), want.view(np.uint32))
+    want = np.concatenate([exp["norm_b%d_image" % k] for k in range(3)])
+    np.testing.assert_array_equal(_run(frames, mean=127.5, std=127.5).cpu().numpy(), want)
+    want = np.concatenate([exp["gamma_b%d_image" % k] for k in range(3)])
+    np.testing.assert_array_equal(_run(frames, gamma=2.2, layout="NHWC", dtype=torch.uint8).cpu().numpy(), want)
+    want = np.concatenate([exp["offscreen_b%d_image" % k] for k in range(3)])
+    np.testing.assert_array_equal(_run(frames, flip=True, gamma=2.2, layout="NHWC", dtype=torch.uint8).cpu().numpy(), want)
+    want = np.concatenate([exp["offscreen_rgb_b%d_image" % k] for k in range(3)])
+    got = _run(np.ascontiguousarray(frames[..., :3]), flip=True, gamma=2.2, layout="NHWC", dtype=torch.uint8)
+    np.testing.assert_array_equal(got.cpu().numpy(), want)
+
+
+def test_variants_agree_and_vector_path_is_taken():
+    from blendtorch.btt import native as N
+    rng = np.random.default_rng(5)
+    for shape in ((4, 48, 64, 4), (2, 16, 64, 3), (3, 10, 32, 1)):
+        frames = rng.integers(0, 256, shape, dtype=np.uint8)
+        for dtype in (torch.float32, torch.bfloat16, torch.uint8):
+            kw = dict(flip=True, gamma=2.2, dtype=dtype)
+            if dtype != torch.uint8:
+                kw.update(mean=127.5, std=127.5)
+            a = _run(frames, variant="generic", **kw)
+            assert N.lib.bt_preprocess_last_variant() == 1
+            b = _run(frames, variant="vector", **kw)
+            assert N.lib.bt_preprocess_last_variant() == 2
+            c = _run(frames, **kw)
+            assert N.lib.bt_preprocess_last_variant() == 2     # auto picks the vector kernel
+            assert torch.equal(a.view(torch.uint8), b.view(torch.uint8))
+            assert torch.equal(a.view(torch.uint8), c.view(torch.uint8))
+    with pytest.raises(N.NativeError):
+        _run(rng.integers(0, 256, (1, 4, 5, 4), dtype=np.uint8), variant="vector")
+
+
+def test_stats_match_oracle_and_are_deterministic():
+    rng = np.random.default_rng(9)
+    frames = rng.integers(0, 256, (6, 40, 64, 4), dtype=np.uint8)
+    for kw in (dict(gamma=2.2, mean=127.5, std=127.5), dict(dtype=torch.uint8, layout="NHWC"),
+               dict(mean=[1., 2., 3., 4.], std=[5., 6., 7., 8.], dtype=torch.bfloat16, out_channels=3)):
+        out, st = _run(frames, stats=True, **kw)
+        s, q = opre.batch_stats(out.float().cpu().numpy() if kw.get("layout") != "NHWC"
+                                else out.float().permute(0, 3, 1, 2).cpu().numpy())
+        got = st.cpu().numpy()
+        np.testing.assert_allclose(got[:, 0], s, rtol=1e-6, atol=1e-3)   # fp32 partial sums of <=64 values
+        np.testing.assert_allclose(got[:, 1], q, rtol=1e-6, atol=1e-3)
+        out2, st2 = _run(frames, stats=True, **kw)
+        assert torch.equal(st, st2)                                        # fixed reduction order
+    # generic variant too
+    out, st = _run(frames[:, :, :5], stats=True, mean=127.5, std=127.5)
+    s, q = opre.batch_stats(out.cpu().numpy())
+    np.testing.assert_allclose(st.cpu().numpy()[:, 0], s, rtol=1e-9, atol=1e-6)
+
+
+def test_empty_and_strided_batches():
+    out = _run(np.zeros((0, 4, 8, 4), np.uint8), mean=127.5, std=127.5)
+    assert out.shape == (0, 4, 4, 8)
+    # frames that sit inside a wider staging buffer (image stride > dense size)
+    rng = np.random.default_rng(1)
+    big = torch.from_numpy(rng.integers(0, 256, (3, 4 * 8 * 4 + 256), dtype=np.uint8)).to(DEV)
+    view = big[:, :4 * 8 * 4].view(3, 4, 8, 4)
+    out = btt.preprocess_images(view, btt.Preprocess(mean=127.5, std=127.5))
+    exp = opre.preprocess_batch(list(view.cpu().numpy()), mean=127.5, std=127.5)
+    np.testing.assert_array_equal(out.cpu().numpy(), exp)
+
+
+def _lut_expected(src, lut_np, flip, chw):
+    """Full-size check: gather through the oracle's 256-entry table with torch ops on the GPU."""
+    B, H, W, C = src.shape
+    lut = torch.from_numpy(lut_np).to(src.device)          # (C, 256)
+    idx = src.long()
+    if flip:
+        idx = idx.flip(1)
+    out = torch.stack([lut[c][idx[..., c]] for c in range(C)], dim=1 if chw else -1)
+    return out
+
+
+@pytest.mark.parametrize("name,shape", [("C2", (8, 480, 640, 4)), ("C3", (32, 1080, 1920, 4)),
+                                        ("C4", (64, 1024, 1024, 4)), ("C5", (1024, 128, 128, 4))])
+def test_full_size_properties(name, shape):
+    """BASELINE.json sizes: (a) exactness against the oracle's per-byte table gathered by torch,
+    (b) flip is an involution, (c) the fused statistics equal torch's own reduction."""
+    g = torch.Generator(device=DEV)
+    g.manual_seed(1234)
+    src = torch.randint(0, 256, shape, dtype=torch.uint8, device=DEV, generator=g)
+    ramp = np.arange(256, dtype=np.uint8).reshape(1, 256, 1).repeat(4, axis=2)
+    lut = opre.preprocess_frame(ramp, gamma=2.2, mean=127.5, std=127.5)[:, 0, :]   # oracle on all 256 bytes
+    spec = btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5, stats=True)
+    out, st = btt.preprocess_images(src, spec)
+    exp = _lut_expected(src, lut, True, True)
+    assert torch.equal(out, exp)
+    tot = out.double().sum(dim=(0, 2, 3))
+    torch.testing.assert_close(st[:, 0], tot, rtol=1e-9, atol=1e-3)
+    del exp, out
+    u8 = btt.Preprocess(flip=True, dtype=torch.uint8, layout="NHWC")
+    twice = btt.preprocess_images(btt.preprocess_images(src, u8), u8)
+    assert torch.equal(twice, src)
+    bf = btt.preprocess_images(src, btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5, dtype=torch.bfloat16))
+    exp = _lut_expected(src, lut, True, True).to(torch.bfloat16)
+    assert torch.equal(bf, exp)
