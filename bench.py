@@ -1,0 +1,437 @@
+#!/usr/bin/env python3
+"""Benchmark of the blendtorch ingest hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json configs[1], the configuration the metric is quoted on):
+RemoteIterableDataset fed by 5 synthetic ZMQ publishers, 640x480 RGBA + bbox annotations,
+batch 8, fused flip + gamma 2.2 + normalise + NHWC->NCHW to fp32 on one B200.
+A step is one pass of the hot path over one batch of 8 frames.
+
+Printed JSON line (rank 0):
+  value      images/s of the device leg: K launches of the fused kernel K1 over batches already
+             resident in HBM (rotating over distinct batches so the working set exceeds L2),
+             replayed from a CUDA graph, timed with CUDA events, max over ranks.
+  e2e        images/s through the public API (btt.DeviceLoader over btt.RemoteIterableDataset)
+             with HOST buffers: ZMQ receive, framing, pinned staging, H2D copy, K1 and a D2H read of
+             the batch statistics are all inside the timed region.
+  roofline   K1 algorithmic bytes per launch (H*W*C*(1 + 4) per image = 20 B/pixel)
+             / average launch duration, against the measured HBM copy peak.
+  cpu_baseline  the oracle port of the reference's CPU path (decode + item_transform + default_collate
+             under torch DataLoader workers) timed on this box's host cores on a bounded sample.
+With --impl reference only that CPU path is run and reported (rank 0 alone under torchrun).
+"""
+import argparse
+import json
+import os
+import signal
+import socket
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+PKG = ROOT / "pytorch-blender_b200"
+for _p in (str(ROOT), str(PKG)):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+H, W, C, BATCH, PUBLISHERS, CONFIG = 480, 640, 4, 8, 5, 2
+GAMMA, MEAN, STD = 2.2, 127.5, 127.5
+WORKLOAD = "C2: 5 synthetic ZMQ publishers, 640x480 RGBA uint8 + bbox, batch 8, flip+gamma2.2+normalise+NCHW fp32"
+METRIC = "images/sec into device tensors (640x480 RGBA, batch 8)"
+ROTATE = 8  # distinct resident batches: 8 x (9.8 MB in + 39.3 MB out) = 393 MB > 126 MB L2
+
+
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def spawn_publishers(module, n, transport="tcp", tag="p"):
+    env = dict(os.environ)
+    env["PYTHONPATH"] = os.pathsep.join([str(ROOT), str(PKG), env.get("PYTHONPATH", "")])
+    addrs, procs = [], []
+    for i in range(n):
+        if transport == "ipc":
+            addr = "ipc:///tmp/bt_bench_%d_%s_%d" % (os.getpid(), tag, i)
+        else:
+            addr = "tcp://127.0.0.1:%d" % free_port()
+        cmd = [sys.executable, "-m", module, "--bind", addr, "--btid", str(i), "--config", str(CONFIG),
+               "--height", str(H), "--width", str(W)]
+        procs.append(subprocess.Popen(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL))
+        addrs.append(addr)
+    return addrs, procs
+
+
+def stop_publishers(procs):
+    for p in procs:
+        try:
+            p.send_signal(signal.SIGTERM)
+        except Exception:
+            pass
+    for p in procs:
+        try:
+            p.wait(timeout=5)
+        except Exception:
+            p.kill()
+
+
+class ClockSampler:
+    """Polls NVML for SM clocks and throttle reasons while a region is marked active."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+               0x4: "sw_power_cap", 0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index):
+        self.samples, self.active, self._stop = [], False, False
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+        self.t = threading.Thread(target=self._run, daemon=True)
+        if self.nv:
+            self.t.start()
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop:
+            if self.active:
+                try:
+                    mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                    try:
+                        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                    except Exception:
+                        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    self.samples.append((mhz, r))
+                except Exception:
+                    pass
+            time.sleep(0.002)
+
+    def report(self):
+        self._stop = True
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        reasons = set()
+        for _, r in self.samples:
+            for bit, name in self.REASONS.items():
+                if r & bit:
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(m for m, _ in self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(reasons), "samples": len(self.samples)}
+
+
+def measured_peaks():
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        try:
+            return float(json.loads(f.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# --------------------------------------------------------------------------------------------
+# CPU path of the reference (oracle port): the cpu_baseline leg and the --impl reference arm.
+# This is the only place bench.py touches oracle/.
+# --------------------------------------------------------------------------------------------
+def _cpu_transform(item):
+    from oracle import preprocess as opre
+    img = opre.flip_vertical(item["image"])          # btb/offscreen.py:95-96
+    img = opre.gamma_correct(img, GAMMA)             # examples/datagen/generate.py:10-14
+    item["image"] = opre.normalise_chw(img)          # examples/densityopt/densityopt.py:117-119
+    return item
+
+
+def _worker_init(_):
+    import torch
+    torch.set_num_threads(1)
+
+
+def run_cpu_reference(steps, warmup, workers, max_seconds=None):
+    """Reference CPU path on this box: synthetic publishers -> (oracle) RemoteIterableDataset port
+    -> item_transform -> default_collate in `workers` DataLoader processes.  Returns
+    (images/s, steps timed, seconds)."""
+    from torch.utils.data import DataLoader
+    from oracle import stream
+    addrs, procs = spawn_publishers("oracle.synth", PUBLISHERS, tag="ref")
+    try:
+        total_batches = steps + warmup
+        per_worker = -(-total_batches // max(workers, 1)) + 2
+        ds = stream.torch_stream_dataset(addrs, max_items=per_worker * BATCH * max(workers, 1),
+                                         item_transform=_cpu_transform, timeoutms=60000)
+        dl = DataLoader(ds, batch_size=BATCH, num_workers=workers, worker_init_fn=_worker_init,
+                        persistent_workers=False, prefetch_factor=4 if workers else None)
+        it = iter(dl)
+        for _ in range(warmup):
+            next(it)
+        t0 = time.perf_counter()
+        done = 0
+        for _ in range(steps):
+            b = next(it)
+            assert b["image"].shape == (BATCH, C, H, W)
+            done += 1
+            if max_seconds and time.perf_counter() - t0 > max_seconds:
+                break
+        dt = time.perf_counter() - t0
+        del it
+        return done * BATCH / dt, done, dt
+    finally:
+        stop_publishers(procs)
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    workers = max(1, min(cores - PUBLISHERS - 1, 64))
+    ips, done, dt = run_cpu_reference(args.steps, args.warmup, workers)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": ips, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": done, "warmup": args.warmup, "ms_per_step": dt / max(done, 1) * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch": BATCH, "publishers": PUBLISHERS,
+                   "transform": "flipud + gamma_correct(2.2) + (x-127.5)/127.5 + CHW, default_collate"},
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": workers, "kind": "port",
+                         "sample": "%d batches of %d through %d DataLoader workers (%d host cpus); oracle port of "
+                                   "btt.RemoteIterableDataset + example item_transforms" % (done, BATCH, workers, cores)},
+        "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------------
+# Our arm
+# --------------------------------------------------------------------------------------------
+def device_leg(torch, btt, dev, steps, warmup, spec, sampler):
+    """K1 over HBM-resident batches.  Returns (seconds for `steps` launches, bytes per launch)."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(2000)
+    srcs = [torch.randint(0, 256, (BATCH, H, W, C), dtype=torch.uint8, device=dev, generator=g) for _ in range(ROTATE)]
+    outs = [torch.empty((BATCH, C, H, W), dtype=torch.float32, device=dev) for _ in range(ROTATE)]
+    stream = torch.cuda.Stream(dev)
+    launches_per_graph = ROTATE
+    with torch.cuda.stream(stream):
+        for i in range(max(warmup, 3)):
+            btt.preprocess_images(srcs[i % ROTATE], spec, out=outs[i % ROTATE])
+        stream.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            for i in range(launches_per_graph):
+                btt.preprocess_images(srcs[i], spec, out=outs[i])
+        graph.replay()
+        stream.synchronize()
+        n_replays, tail = divmod(steps, launches_per_graph)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.active = True
+        e0.record(stream)
+        for _ in range(n_replays):
+            graph.replay()
+        for i in range(tail):
+            btt.preprocess_images(srcs[i], spec, out=outs[i])
+        e1.record(stream)
+        e1.synchronize()
+        sampler.active = False
+    sec = e0.elapsed_time(e1) * 1e-3
+    algo_bytes = BATCH * H * W * C * (1 + 4)
+    return sec, algo_bytes
+
+
+def large_batch_probe(torch, btt, dev, spec):
+    """Same kernel on BASELINE config 4's per-GPU batch (64 x 1024x1024 RGBA), where launch ramp and
+    tail are amortised: reported beside the headline roofline, not instead of it."""
+    B2, H2, W2 = 64, 1024, 1024
+    g = torch.Generator(device=dev)
+    g.manual_seed(4000)
+    src = torch.randint(0, 256, (B2, H2, W2, C), dtype=torch.uint8, device=dev, generator=g)
+    out = torch.empty((B2, C, H2, W2), dtype=torch.float32, device=dev)
+    for _ in range(3):
+        btt.preprocess_images(src, spec, out=out)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 20
+    e0.record()
+    for _ in range(reps):
+        btt.preprocess_images(src, spec, out=out)
+    e1.record()
+    e1.synchronize()
+    sec = e0.elapsed_time(e1) * 1e-3 / reps
+    return B2 * H2 * W2 * C * 5 / sec / 1e9, sec
+
+
+def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers):
+    """Public API with host buffers: publishers -> DeviceLoader -> device batch (+ stats read back)."""
+    addrs, procs = spawn_publishers("blendtorch.btt.synthetic", PUBLISHERS, transport, tag="r%s" % os.environ.get("RANK", "0"))
+    try:
+        total = (steps + warmup) * BATCH
+        per_recv = -(-(steps + warmup) // receivers) * BATCH
+        ds = btt.RemoteIterableDataset(addrs, max_items=per_recv * receivers + 0, timeoutms=60000)
+        spec = btt.Preprocess(key="image", flip=True, gamma=GAMMA, mean=MEAN, std=STD, stats=True)
+        dl = btt.DeviceLoader(ds, batch_size=BATCH, device=dev, preprocess=spec, num_receivers=receivers,
+                              ring_depth=4, prefetch=4)
+        it = iter(dl)
+        h2d = d2h = 0
+        for _ in range(warmup):
+            b = next(it)
+            b["image_stats"].cpu()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.active = True
+        t0 = time.perf_counter()
+        e0.record()
+        images = 0
+        for _ in range(steps):
+            b = next(it)
+            st = b["image_stats"].cpu()          # D2H read of the step's result
+            images += b["image"].shape[0]
+        e1.record()
+        e1.synchronize()
+        wall = time.perf_counter() - t0
+        sampler.active = False
+        sec = e0.elapsed_time(e1) * 1e-3
+        h2d = sum(v.numel() * v.element_size() for k, v in b.items()
+                  if isinstance(v, torch.Tensor) and k in ("btid", "frameid", "bbox")) + BATCH * H * W * C
+        d2h = st.numel() * st.element_size()
+        it.close() if hasattr(it, "close") else None
+        del it
+        _ = total
+        return images, max(sec, wall), h2d, d2h
+    finally:
+        stop_publishers(procs)
+
+
+def ours(args):
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    import importlib.util
+    spec_ = importlib.util.spec_from_file_location("bt_build_native", PKG / "build_native.py")
+    mod = importlib.util.module_from_spec(spec_)
+    spec_.loader.exec_module(mod)
+    if not mod.LIB.exists():
+        mod.build()
+    from blendtorch import btt
+    from blendtorch.btt import native as N
+    import ctypes
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    sampler = ClockSampler(local)
+    h2d_gbs = ctypes.c_double(0.0)
+    N.check(N.lib.bt_measure_h2d(local, 64 << 20, 20, ctypes.byref(h2d_gbs)))
+
+    spec = btt.Preprocess(key="image", flip=True, gamma=GAMMA, mean=MEAN, std=STD)
+    barrier()
+    sec, algo_bytes = device_leg(torch, btt, dev, args.steps, args.warmup, spec, sampler)
+    barrier()
+    sec = max_over_ranks(sec)
+    value = world * args.steps * BATCH / sec
+    achieved = algo_bytes * args.steps / (sec if world == 1 else sec) / 1e9
+    large_gbs, large_sec = large_batch_probe(torch, btt, dev, spec) if rank == 0 else (0.0, 0.0)
+
+    barrier()
+    images, e2e_sec, h2d, d2h = e2e_leg(torch, btt, dev, args.steps, args.warmup, sampler, args.transport, args.receivers)
+    barrier()
+    e2e_sec = max_over_ranks(e2e_sec)
+    images = sum_over_ranks(images)
+    e2e_value = images / e2e_sec
+    clocks = sampler.report()
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        workers = max(1, min(cores - PUBLISHERS - 1, 64))
+        ips, done, dt = run_cpu_reference(steps=100000, warmup=2, workers=workers, max_seconds=15.0)
+        cpu = {"value": ips, "unit": "images/s", "cores": workers, "kind": "port",
+               "sample": "%d batches of %d in %.1f s through %d DataLoader workers (%d host cpus); oracle port of "
+                         "btt.RemoteIterableDataset + flipud/gamma/normalise item_transform + default_collate"
+                         % (done, BATCH, dt, workers, cores)}
+    if rank == 0:
+        peak, peak_src = measured_peaks()
+        h2d_bytes_img = H * W * C
+        line = {
+            "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch": BATCH, "publishers": PUBLISHERS,
+                       "l2": "device leg rotates over %d distinct resident batches (%.0f MB working set > 126 MB L2), "
+                             "launches replayed from a CUDA graph" % (ROTATE, ROTATE * BATCH * H * W * C * 5 / 1e6),
+                       "e2e_transport": args.transport, "e2e_receivers": args.receivers,
+                       "parallelism": "dp%d, publishers sharded per GPU, no collective" % world},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "k1_planar<float,4,4,4>", "algorithmic_bytes_per_launch": algo_bytes,
+                         "frac_of_nominal_8TBs": achieved / 8000.0,
+                         "large_batch": {"workload": "C4 per-GPU batch: 64 x 1024x1024 RGBA -> fp32 NCHW",
+                                         "achieved": large_gbs, "frac": large_gbs / peak, "ms": large_sec * 1e3}},
+            "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "gbs_h2d": e2e_value * h2d_bytes_img / 1e9 / world, "pcie_h2d_measured_gbs": h2d_gbs.value,
+                    "frac_of_pcie_h2d": e2e_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value},
+            "gpu_launches": args.steps, "gpu_launches_e2e": args.steps,
+            "clocks": clocks,
+            "cpu_baseline": cpu,
+            "host": {"cpus": os.cpu_count()},
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--transport", default="tcp", choices=["tcp", "ipc"])
+    ap.add_argument("--receivers", type=int, default=4)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        return reference_arm(args)
+    return ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

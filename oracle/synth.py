@@ -70,3 +70,36 @@ def message(rng, config, btid, frameid, h, w, c=4):
 
 def pickled(msg, protocol=3):
     return pickle.dumps(msg, protocol=protocol)
+
+
+def run_publisher(bind, btid, config, h, w, c=4, count=-1, pool=16, protocol=3):
+    """Endless (count < 0) synthetic publisher for the CPU-baseline / reference arm of bench.py:
+    the restated btb publisher (oracle/stream.py) fed from a pre-pickled pool so that the
+    producer costs a send, not a render."""
+    from .stream import Publisher
+
+    rng = rng_for(config, btid)
+    blobs = [pickled(message(rng, config, btid, i, h, w, c), protocol) for i in range(pool)]
+    pub = Publisher(bind, btid=btid, send_hwm=10, lingerms=0)
+    i = 0
+    try:
+        while count < 0 or i < count:
+            pub.sock.send(blobs[i % pool], copy=False)
+            i += 1
+    finally:
+        pub.close()
+
+
+if __name__ == "__main__":
+    import argparse
+
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--bind", required=True)
+    ap.add_argument("--btid", type=int, default=0)
+    ap.add_argument("--config", type=int, default=2)
+    ap.add_argument("--height", type=int, default=480)
+    ap.add_argument("--width", type=int, default=640)
+    ap.add_argument("--count", type=int, default=-1)
+    ap.add_argument("--pool", type=int, default=16)
+    a = ap.parse_args()
+    run_publisher(a.bind, a.btid, a.config, a.height, a.width, 4, a.count, a.pool)

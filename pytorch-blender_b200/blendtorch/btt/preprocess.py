@@ -105,6 +105,12 @@ def preprocess_images(src, spec, out=None, stream=None, stats_out=None, _scratch
         if tuple(out.shape) != shape or out.dtype != spec.dtype or not out.is_contiguous():
             raise ValueError("out must be a contiguous %s tensor of shape %s" % (spec.dtype, shape))
 
+    if out.numel() == 0:  # nothing to launch for an empty batch
+        if spec.stats:
+            st = stats_out if stats_out is not None else torch.empty((cout, 2), dtype=torch.float64, device=src.device)
+            return out, st.zero_()
+        return out
+
     p = N.PreprocessParams()
     p.src = src.data_ptr()
     p.dst = out.data_ptr()

@@ -83,8 +83,8 @@ def test_shuffle_drop_last_and_item_transform(golden_dir):
     np.testing.assert_array_equal(b["image"][1].cpu().numpy(), opre.preprocess_frame(raw, mean=127.5, std=127.5))
 
 
-def _publisher(addr, btid, count, h, w, cfg, proto):
-    S.run_publisher(addr, btid, cfg, h, w, 4, count=count, pool=count, protocol=proto, lingerms=10000)
+def _publisher(addr, btid, count, pool, h, w, cfg, proto):
+    S.run_publisher(addr, btid, cfg, h, w, 4, count=count, pool=pool, protocol=proto, lingerms=10000)
 
 
 @pytest.mark.parametrize("receivers", [1, 2])
@@ -92,7 +92,7 @@ def test_stream_exactly_once_and_values(receivers, tmp_path):
     H, W, per_pub, pubs = 24, 32, 12, 2
     addrs = ["tcp://127.0.0.1:%d" % _free_port() for _ in range(pubs)]
     ctx = mp.get_context("spawn")
-    procs = [ctx.Process(target=_publisher, args=(a, i, -1 if receivers > 1 else per_pub, H, W, 2, 3 + i), daemon=True)
+    procs = [ctx.Process(target=_publisher, args=(a, i, -1 if receivers > 1 else per_pub, per_pub, H, W, 2, 3 + i), daemon=True)
              for i, a in enumerate(addrs)]
     for p in procs:
         p.start()
@@ -120,11 +120,13 @@ def test_stream_exactly_once_and_values(receivers, tmp_path):
         # every delivered frame is byte-identical to what the publisher generated
         for btid in range(pubs):
             rng = S.rng_for(2, btid)
-            msgs = [S.message(rng, 2, btid, i, H, W) for i in range(per_pub if receivers == 1 else 0)]
-            for i, m in enumerate(msgs):
+            msgs = [S.message(rng, 2, btid, i, H, W) for i in range(per_pub)]
+            keys = [k for k in got if k[0] == btid]
+            assert keys
+            for (_, i) in keys:
                 raw, bbox = got[(btid, i)]
-                np.testing.assert_array_equal(raw, m["image"])
-                np.testing.assert_array_equal(bbox, m["bbox"])
+                np.testing.assert_array_equal(raw, msgs[i]["image"])
+                np.testing.assert_array_equal(bbox, msgs[i]["bbox"])
         if receivers == 1:
             assert len(got) == total                      # exactly once
         # the tee recorded every raw message; replaying it gives the same frames
