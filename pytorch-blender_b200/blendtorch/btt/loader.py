@@ -113,13 +113,15 @@ class DeviceLoader:
         workers (dataset.py:80-85,97).
     ring_depth: pinned slots per receiver.  prefetch: finished batches queued ahead of the consumer.
     ingest_threads: host threads `bt_schema_ingest_many` uses per replay batch.
+    io_threads: ZMQ I/O threads per receiver; a receiver's connections (one per publisher) are
+        spread over them, so socket reads of different publishers proceed in parallel.
     seed: shuffle seed (epoch number is added on every new iteration).
     keep_raw: also return the untouched uint8 frames as ``<key>_raw``.
     """
 
     def __init__(self, dataset, batch_size=1, shuffle=False, drop_last=False, device="cuda",
                  preprocess=None, num_receivers=1, ring_depth=3, prefetch=2, ingest_threads=4,
-                 seed=0, keep_raw=False):
+                 seed=0, keep_raw=False, io_threads=1):
         self.dataset = dataset
         self.batch_size = int(batch_size)
         if self.batch_size < 1:
@@ -140,6 +142,7 @@ class DeviceLoader:
         self.ring_depth, self.prefetch = int(ring_depth), int(prefetch)
         self.ingest_threads = int(ingest_threads)
         self.seed, self.keep_raw = seed, keep_raw
+        self.io_threads = max(1, int(io_threads))
         self._epoch = 0
         self.stats = {"batches": 0, "items": 0, "bytes_h2d": 0, "kernels": 0, "compat_items": 0}
         if isinstance(dataset, RemoteIterableDataset):
@@ -184,7 +187,7 @@ class DeviceLoader:
     def _stream_producer(self, rid, out_q, stop):
         ds = self.dataset
         stager = None
-        ctx = zmq.Context()
+        ctx = zmq.Context(io_threads=self.io_threads)
         sock = None
         rec = None
         try:
