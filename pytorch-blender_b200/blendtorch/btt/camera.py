@@ -79,6 +79,8 @@ class Camera:
             out["bbox"] = torch.empty((B, Np // bbox_corners, 4), dtype=torch.float64, device=self.device)
             p.bbox_out = out["bbox"].data_ptr()
             p.corners_per_object = bbox_corners
+        if B * Np == 0:  # nothing to project
+            return out
         with torch.cuda.device(self.device):
             N.check(N.lib.bt_project_launch(C.byref(p), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
         return out
