@@ -204,6 +204,29 @@ int bt_preprocess_launch(const bt_preprocess_params* p, void* stream);
 /* How many kernels the last bt_preprocess_launch on this thread enqueued and which variant ran. */
 int bt_preprocess_last_variant(void);
 
+/* K1 with per-batch statistics for callers that cannot allocate device memory.
+ * (No counterpart in the reference: it never touches the device.)
+ *
+ * Same semantics and same kernel as bt_preprocess_launch with `stats_out` set, but the scratch
+ * the statistics need (per-CTA partial sums + an arrival counter) is a fixed array compiled into
+ * the library instead of caller memory, and the call performs no cudaMalloc / cudaFree or any
+ * other allocating routine.  Meant for hosts that give a plug-in a fixed device-memory budget,
+ * for ingest loops that may not call an allocator after start-up, and for processes sharing a
+ * GPU whose memory another framework has already claimed.  The caller still passes src, dst
+ * and stats_out; `stats_scratch` in the params is ignored.
+ *
+ * Limits and rules:
+ *  - batch*height*width*channels must not exceed 19 398 656 bytes (1184 rows of partial sums,
+ *    one per 16 KiB of input); larger batches fail with BT_E_TOO_LARGE and a message saying so.
+ *  - The array costs 76 032 bytes on every GPU that loads the library, until the process exits.
+ *  - The first call on each device resolves the array's device address (and, like any first
+ *    launch, loads the kernels); make that first call before starting any stream capture.
+ *  - All calls on a device share the one array.  The arrival counter is zeroed on `stream` before
+ *    every launch and the partial sums are rewritten before they are read, so back-to-back calls
+ *    on one stream are fine; calls whose kernels can overlap on the GPU (different streams or
+ *    threads without ordering between them) race on it and give wrong statistics. */
+int bt_preprocess_stats_static(const bt_preprocess_params* p, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * K2: batched annotation projection world -> NDC -> pixel (+ linear depth, + pixel bboxes).
  * Replaces Camera.world_to_ndc  pkg_blender/blendtorch/btb/camera.py:84-112,

@@ -101,6 +101,7 @@ def _load():
         "bt_preprocess_scratch_bytes": (u64, [C.POINTER(PreprocessParams)]),
         "bt_preprocess_launch": (i32, [C.POINTER(PreprocessParams), vp]),
         "bt_preprocess_last_variant": (i32, []),
+        "bt_preprocess_stats_static": (i32, [C.POINTER(PreprocessParams), vp]),
         "bt_project_launch": (i32, [C.POINTER(ProjectParams), vp]),
         "bt_device_count": (i32, [C.POINTER(i32)]),
         "bt_measure_h2d": (i32, [i32, u64, i32, C.POINTER(C.c_double)]),
@@ -119,7 +120,7 @@ EXPORTS = ["bt_last_error", "bt_abi_version", "bt_scan_message", "bt_schema_crea
            "bt_schema_ingest_many", "bt_ring_create", "bt_ring_destroy", "bt_ring_depth",
            "bt_ring_slot_bytes", "bt_ring_slot_ptr", "bt_ring_acquire", "bt_ring_submit", "bt_ring_wait",
            "bt_build_gamma_lut", "bt_preprocess_scratch_bytes", "bt_preprocess_launch",
-           "bt_preprocess_last_variant", "bt_project_launch", "bt_device_count", "bt_measure_h2d"]
+           "bt_preprocess_last_variant", "bt_preprocess_stats_static", "bt_project_launch", "bt_device_count", "bt_measure_h2d"]
 
 
 def last_error():

@@ -466,3 +466,81 @@ int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// bt_preprocess_stats_static: K1 with statistics for callers that must not allocate.
+//
+// The statistics reduction needs a little device memory besides the caller's input, output
+// and stats_out: one row of partial sums per CTA plus an arrival counter.  The regular entry
+// point takes that memory from the caller (`stats_scratch`), which means somebody has to
+// cudaMalloc it.  Some users of this library cannot: a render or simulation plug-in that is
+// handed a fixed device-memory budget by its host application, a real-time ingest loop whose
+// rules forbid allocator calls after start-up, a process running next to a framework that
+// already owns all free memory of the GPU.  For them the scratch lives in the array below,
+// which is part of the library image: every GPU whose context loads libbt_b200.so holds these
+// 76 032 bytes until the process exits, whether or not this entry point is ever called.
+//
+// `g_static_stats_scratch` as written in host code is only a host-side handle for the symbol,
+// not a device address; the address a kernel may use is looked up once per device with
+// cudaGetSymbolAddress (that device current) and cached.
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace {
+constexpr int kStaticRows = kStatsMaxGrid;                       // partial-sum rows in the static array
+constexpr uint64_t kStaticScratchBytes = (uint64_t)kStaticRows * kMaxC * 2 * sizeof(double) + 256;
+constexpr uint64_t kStaticBytesPerRow = 16384;                   // input bytes covered by one CTA's row
+constexpr uint64_t kStaticMaxInputBytes = (uint64_t)kStaticRows * kStaticBytesPerRow;  // 19 398 656
+constexpr int kMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_static_stats_scratch[kStaticScratchBytes];
+
+namespace {
+std::mutex g_static_mu;
+void* g_static_addr[kMaxDevices] = {nullptr};
+
+// Device address of the static scratch on the current device; first use per device resolves it.
+int static_scratch_address(void** out) {
+  int dev = -1;
+  BT_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return bt::fail(BT_E_INVALID, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_addr[dev]) {
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_stats_scratch);
+    if (e != cudaSuccess || !ptr)
+      return bt::fail(BT_E_CUDA, "cudaGetSymbolAddress(static scratch) on device %d failed: %s", dev,
+                      cudaGetErrorString(e));
+    g_static_addr[dev] = ptr;
+  }
+  *out = g_static_addr[dev];
+  return BT_OK;
+}
+}  // namespace
+
+extern "C" int bt_preprocess_stats_static(const bt_preprocess_params* p, void* stream) {
+  if (!p) return bt::fail(BT_E_INVALID, "bt_preprocess_stats_static: null pointer");
+  if (!p->stats_out)
+    return bt::fail(BT_E_INVALID, "bt_preprocess_stats_static computes statistics: stats_out must be set "
+                                  "(without statistics bt_preprocess_launch needs no scratch at all)");
+  if (p->batch < 0 || p->height < 0 || p->width < 0 || p->channels < 1 || p->channels > kMaxC)
+    return bt::fail(BT_E_INVALID, "bt_preprocess_stats_static: bad extents");
+  const uint64_t in_bytes = (uint64_t)p->batch * p->height * p->width * p->channels;
+  if (in_bytes > kStaticMaxInputBytes)
+    return bt::fail(BT_E_TOO_LARGE,
+                    "batch of %llu input bytes exceeds the %llu bytes the built-in scratch covers (%d rows of "
+                    "partial sums, one per %llu input bytes); split the batch or use bt_preprocess_launch "
+                    "with caller-provided stats_scratch",
+                    (unsigned long long)in_bytes, (unsigned long long)kStaticMaxInputBytes, kStaticRows,
+                    (unsigned long long)kStaticBytesPerRow);
+  void* scratch = nullptr;
+  int rc = static_scratch_address(&scratch);
+  if (rc != BT_OK) return rc;
+  bt_preprocess_params q = *p;
+  q.stats_scratch = scratch;  // same kernel, same launch path; only the scratch differs
+  // bt_preprocess_launch zeroes the arrival counter (cudaMemsetAsync on `stream`) before every
+  // launch, so whatever an earlier call left in the shared array does not matter; the partial
+  // rows are fully overwritten by the CTAs that are launched before anything reads them.
+  return bt_preprocess_launch(&q, stream);
+}
