@@ -126,9 +126,13 @@ class SingleFileDataset(tud.Dataset):
 class FileDataset(tud.ConcatDataset):
     """Replays all recordings ``{record_path_prefix}_*.btr`` as one dataset (dataset.py:134-153)."""
 
-    def __init__(self, record_path_prefix, item_transform=None):
+    def __init__(self, record_path_prefix, item_transform=None, *, rank=None, world_size=None):
         fnames = sorted(glob(f"{record_path_prefix}_*.btr"))
         assert len(fnames) > 0, f"Found no recording files with prefix {record_path_prefix}"
+        if world_size is not None:
+            # one process per GPU: rank k replays files k::G of the sorted glob (no collective)
+            fnames = fnames[(rank or 0)::world_size]
+            assert len(fnames) > 0, f"No recording files left for rank {rank} of {world_size}"
         super().__init__([SingleFileDataset(f) for f in fnames])
         self.filenames = fnames
         self.item_transform = item_transform or _identity_item_transform
