@@ -139,11 +139,33 @@ __device__ void finish_stats(const K1Args& a, StatAcc& acc) {
   __syncthreads();
   if (!last) return;
   __threadfence();
-  if (threadIdx.x < a.Cout * 2) {
-    int c = threadIdx.x >> 1, k = threadIdx.x & 1;
+  // Fold the rows with the whole CTA, still in a fixed order: thread t owns value (t & 7) of rows
+  // t>>3, t>>3 + 32, ... (coalesced 2 KB per step), then lane groups are folded in index order.
+  {
+    constexpr int kVals = kMaxC * 2;            // 8 doubles per row
+    constexpr int kGroups = kThreads / kVals;   // 32 row groups
+    const int v = threadIdx.x & (kVals - 1), grp = threadIdx.x >> 3;
     double t = 0.0;
-    for (unsigned b = 0; b < gridDim.x; ++b) t += __ldcg(&a.partials[((size_t)b * kMaxC + c) * 2 + k]);
-    a.stats_out[c * 2 + k] = t;
+    constexpr int kInFlight = 8;                // independent loads per step: the fold is latency-bound
+    for (unsigned b0 = grp; b0 < gridDim.x; b0 += kGroups * kInFlight) {
+      double r[kInFlight];
+#pragma unroll
+      for (int j = 0; j < kInFlight; ++j) {
+        const unsigned b = b0 + j * kGroups;
+        r[j] = b < gridDim.x ? __ldcg(&a.partials[(size_t)b * kVals + v]) : 0.0;
+      }
+#pragma unroll
+      for (int j = 0; j < kInFlight; ++j) t += r[j];
+    }
+    __shared__ double grp_sum[kGroups][kVals];
+    grp_sum[grp][v] = t;
+    __syncthreads();
+    if (threadIdx.x < kVals) {
+      double s = 0.0;
+      for (int g2 = 0; g2 < kGroups; ++g2) s += grp_sum[g2][threadIdx.x];
+      const int c = threadIdx.x >> 1, k = threadIdx.x & 1;
+      if (c < (int)a.Cout) a.stats_out[c * 2 + k] = s;
+    }
   }
   if (threadIdx.x == 0) *a.ticket = 0;  // ready for the next launch
 }

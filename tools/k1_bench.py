@@ -1,0 +1,97 @@
+#!/usr/bin/env python3
+"""Micro-benchmark of K1 variants (diagnostic): per-launch time from CUDA-graph replays over rotating
+buffers larger than L2.  Usage: python tools/k1_bench.py [quick]"""
+import json
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path[:0] = [str(ROOT), str(ROOT / "pytorch-blender_b200")]
+import torch  # noqa: E402
+
+from blendtorch import btt  # noqa: E402
+
+DEV = torch.device("cuda", 0)
+ESZ = {torch.float32: 4, torch.bfloat16: 2, torch.uint8: 1}
+
+
+def run(shape, dtype, layout="NCHW", stats=False, variant="auto", gamma=2.2, norm=True, streams=1, reps=200,
+        smooth=False):
+    B, H, W, C = shape
+    in_b = B * H * W * C
+    out_b = in_b * ESZ[dtype]
+    rot = max(2, int(400e6 // (in_b + out_b)) + 1)
+    g = torch.Generator(device=DEV)
+    g.manual_seed(1)
+    if smooth:
+        base = torch.arange(W, device=DEV).view(1, 1, W, 1) // 3 + torch.arange(H, device=DEV).view(1, H, 1, 1) // 2
+        srcs = [((base + i) % 256).to(torch.uint8).expand(B, H, W, C).contiguous() for i in range(rot)]
+    else:
+        srcs = [torch.randint(0, 256, shape, dtype=torch.uint8, device=DEV, generator=g) for _ in range(rot)]
+    oshape = (B, C, H, W) if layout == "NCHW" else (B, H, W, C)
+    outs = [torch.empty(oshape, dtype=dtype, device=DEV) for _ in range(rot)]
+    kw = dict(flip=True, gamma=gamma, layout=layout, dtype=dtype, stats=stats, variant=variant)
+    if norm and dtype != torch.uint8:
+        kw.update(mean=127.5, std=127.5)
+    spec = btt.Preprocess(**kw)
+    scratch = torch.empty(1 << 17, dtype=torch.uint8, device=DEV)
+    st_out = torch.empty((C, 2), dtype=torch.float64, device=DEV)
+    ss = [torch.cuda.Stream(DEV) for _ in range(streams)]
+    main = ss[0]
+
+    def launch(i, s):
+        btt.preprocess_images(srcs[i], spec, out=outs[i], stream=s, stats_out=st_out, _scratch=scratch)
+
+    with torch.cuda.stream(main):
+        for i in range(3):
+            launch(i % rot, main)
+        main.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=main):
+            if streams > 1:
+                ev0 = torch.cuda.Event()
+                ev0.record(main)
+                for s in ss[1:]:
+                    s.wait_event(ev0)
+            for i in range(rot):
+                launch(i, ss[i % streams])
+            if streams > 1:
+                for s in ss[1:]:
+                    e = torch.cuda.Event()
+                    e.record(s)
+                    main.wait_event(e)
+        graph.replay()
+        main.synchronize()
+        n = max(1, reps // rot)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(main)
+        for _ in range(n):
+            graph.replay()
+        e1.record(main)
+        e1.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / (n * rot)
+    return {"shape": list(shape), "dtype": str(dtype).split(".")[-1], "layout": layout, "stats": stats,
+            "variant": variant, "streams": streams, "smooth": smooth, "us": round(us, 2),
+            "GBps": round((in_b + out_b) / us / 1e3, 1), "frac_meas": round((in_b + out_b) / us / 1e3 / 6548.5, 3)}
+
+
+def main():
+    C2, C4, C5, C3 = (8, 480, 640, 4), (64, 1024, 1024, 4), (1024, 128, 128, 4), (32, 1080, 1920, 4)
+    cases = [
+        dict(shape=C2, dtype=torch.float32), dict(shape=C2, dtype=torch.float32, streams=2),
+        dict(shape=C2, dtype=torch.float32, streams=4), dict(shape=C2, dtype=torch.float32, stats=True),
+        dict(shape=C2, dtype=torch.float32, smooth=True),
+        dict(shape=C2, dtype=torch.bfloat16), dict(shape=C2, dtype=torch.uint8, layout="NHWC"),
+        dict(shape=C4, dtype=torch.float32), dict(shape=C4, dtype=torch.float32, stats=True),
+        dict(shape=C4, dtype=torch.float32, smooth=True),
+        dict(shape=C4, dtype=torch.bfloat16), dict(shape=C4, dtype=torch.uint8, layout="NHWC"),
+        dict(shape=C4, dtype=torch.float32, layout="NHWC"),
+        dict(shape=C3, dtype=torch.float32), dict(shape=C5, dtype=torch.float32),
+        dict(shape=(8, 480, 640, 3), dtype=torch.float32), dict(shape=(8, 481, 641, 4), dtype=torch.float32),
+    ]
+    for c in cases:
+        print(json.dumps(run(**c)), flush=True)
+
+
+if __name__ == "__main__":
+    main()
