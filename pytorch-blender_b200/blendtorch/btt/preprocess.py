@@ -54,6 +54,7 @@ class Preprocess:
     out_channels: Optional[int] = None
     stats: bool = False
     variant: str = "auto"
+    tune: int = 0   # developer knob: low byte = units per thread, next byte = CTAs per SM cap (0 = defaults)
     _lut: bytes = field(default=b"", repr=False)
 
     def __post_init__(self):
@@ -122,6 +123,7 @@ def preprocess_images(src, spec, out=None, stream=None, stats_out=None, _scratch
     p.use_gamma = int(bool(spec.gamma))
     p.use_norm = int(spec.mean is not None or spec.std is not None)
     p.variant = VARIANTS[spec.variant]
+    p.reserved = int(spec.tune)
     p.src_image_stride = src.stride(0) if B > 1 else 0
     mean, std = _per_channel(spec.mean, 0.0), _per_channel(spec.std, 1.0)
     for c in range(4):

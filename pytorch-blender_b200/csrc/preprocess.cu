@@ -23,6 +23,10 @@
 namespace {
 
 constexpr int kThreads = 256;
+// Grid cap in CTAs per SM.  Measured on B200 (profiles/r1_k1_tuning.txt): a grid that covers the
+// batch in one pass per thread beats a persistent grid-stride loop (0.97 vs 0.85 of the measured
+// HBM peak at 64 x 1024^2 RGBA), so the cap only guards against absurd grids.
+constexpr int kDefaultCtasPerSm = 128;
 constexpr int kMaxC = 4;
 
 struct K1Args {
@@ -202,51 +206,76 @@ __global__ void __launch_bounds__(kThreads) k1_generic(K1Args a) {
 }
 
 // ---- variant 2: register-vectorised, planar (CHW) output ---------------------------------------
-// One "unit" is PPT consecutive pixels of one row: PPT*C bytes in (16-byte loads), PPT values out
-// per plane (16-byte stores where PPT*sizeof(T) allows).  A warp therefore reads 32*PPT*C
-// contiguous bytes and writes 32*PPT*sizeof(T) contiguous bytes per plane.  UNROLL units per
-// thread are loaded before any is consumed, to keep >= UNROLL*PPT*C bytes in flight per thread.
+// One "unit" is PPT consecutive pixels of one row: PPT*C bytes in (the widest aligned loads that
+// divide it: 16, 8 or 4 bytes), PPT values out per plane (16-byte stores where PPT*sizeof(T)
+// allows).  A warp therefore reads 32*PPT*C contiguous bytes and writes 32*PPT*sizeof(T)
+// contiguous bytes per plane.  UNROLL units per thread are loaded before any is consumed, to keep
+// UNROLL*PPT*C bytes in flight per thread.  Index arithmetic is 32-bit with host-computed
+// multiply-shift division (the launcher keeps units per launch below 2^31).
+struct FastDiv {
+  uint32_t mul, shift, div;
+};
+__device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv& d) {
+  return (__umulhi(n, d.mul) + n) >> d.shift;
+}
+
+struct PlanarGeom {
+  FastDiv upr;   // units per row
+  FastDiv rows;  // rows per image (H)
+  uint32_t total_units;
+};
+
+template <int LW>
+__device__ __forceinline__ void ld_words(const uint8_t* p, uint32_t* w) {
+  if constexpr (LW == 16) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p));
+  } else if constexpr (LW == 8) {
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(w[0]), "=r"(w[1]) : "l"(p));
+  } else {
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(w[0]) : "l"(p));
+  }
+}
+
 template <typename T, int C, int PPT, int UNROLL, bool STATS>
-__global__ void __launch_bounds__(kThreads) k1_planar(K1Args a) {
-  static_assert((PPT * C) % 16 == 0, "unit must be whole 16-byte loads");
-  constexpr int LOADS = PPT * C / 16;
+__global__ void __launch_bounds__(kThreads) k1_planar(K1Args a, PlanarGeom g) {
+  constexpr int UB = PPT * C;                              // unit bytes
+  constexpr int LW = (UB % 16 == 0) ? 16 : (UB % 8 == 0) ? 8 : 4;
+  static_assert(UB % 4 == 0, "unit must be whole 32-bit words");
+  constexpr int WORDS = UB / 4;
   __shared__ T lut[kMaxC * 256];
   build_lut<T>(a, lut);
   StatAcc acc;
   if (STATS) acc.clear();
 
-  const uint32_t upr = a.W / PPT;                     // units per row
-  const uint64_t rows = (uint64_t)a.B * a.H;
-  const uint64_t total = rows * upr;
-  const uint64_t plane = (uint64_t)a.H * a.W;
+  const uint32_t plane = a.H * a.W;                        // < 2^30 (checked by the launcher)
   T* dst = static_cast<T*>(a.dst);
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint32_t stride = gridDim.x * blockDim.x;
 
-  for (uint64_t u0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; u0 < total; u0 += stride * UNROLL) {
-    uint4 in[UNROLL][LOADS];
+  for (uint32_t u0 = blockIdx.x * blockDim.x + threadIdx.x; u0 < g.total_units; u0 += stride * UNROLL) {
+    uint32_t in[UNROLL][WORDS];
     uint64_t out_off[UNROLL];
     bool live[UNROLL];
 #pragma unroll
     for (int j = 0; j < UNROLL; ++j) {
-      uint64_t u = u0 + (uint64_t)j * stride;
-      live[j] = u < total;
+      const uint32_t u = u0 + j * stride;
+      live[j] = u < g.total_units && u >= u0;              // (second test: wrap-around guard)
       if (live[j]) {
-        uint64_t row = u / upr;
-        uint32_t ux = (uint32_t)(u - row * upr);
-        uint32_t b = (uint32_t)(row / a.H);
-        uint32_t y = (uint32_t)(row - (uint64_t)b * a.H);
-        uint32_t sy = a.flip ? a.H - 1 - y : y;
-        const uint4* sp = reinterpret_cast<const uint4*>(
-            a.src + (uint64_t)b * a.src_image_stride + ((uint64_t)sy * a.W + (uint64_t)ux * PPT) * C);
+        const uint32_t row = fdiv(u, g.upr);
+        const uint32_t ux = u - row * g.upr.div;
+        const uint32_t b = fdiv(row, g.rows);
+        const uint32_t y = row - b * g.rows.div;
+        const uint32_t sy = a.flip ? a.H - 1 - y : y;
+        const uint8_t* sp = a.src + (uint64_t)b * a.src_image_stride + ((uint64_t)sy * a.W + (uint64_t)ux * PPT) * C;
 #pragma unroll
-        for (int l = 0; l < LOADS; ++l) in[j][l] = ld_stream(sp + l);
-        out_off[j] = (uint64_t)b * a.Cout * plane + (uint64_t)y * a.W + (uint64_t)ux * PPT;
+        for (int l = 0; l < UB / LW; ++l) ld_words<LW>(sp + l * LW, &in[j][l * (LW / 4)]);
+        out_off[j] = ((uint64_t)b * a.Cout) * plane + (uint64_t)y * a.W + (uint64_t)ux * PPT;
       }
     }
 #pragma unroll
     for (int j = 0; j < UNROLL; ++j) {
       if (!live[j]) continue;
-      const uint32_t* words = reinterpret_cast<const uint32_t*>(&in[j][0]);
+      const uint32_t* words = in[j];
 #pragma unroll
       for (int c = 0; c < C; ++c) {
         if (c < (int)a.Cout) {
@@ -267,51 +296,53 @@ __global__ void __launch_bounds__(kThreads) k1_planar(K1Args a) {
 }
 
 // ---- variant 2b: register-vectorised, interleaved (HWC) output ---------------------------------
-// Rows are streams of W*C bytes; a unit is 16 bytes of one row.  Needs Cout == C.
-template <typename T, int UNROLL, bool STATS>
-__global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a) {
+// Rows are streams of W*C bytes.  A unit is IB = 16/sizeof(T) input bytes of one row, so that every
+// thread's result is exactly one 16-byte store and a warp writes 512 contiguous bytes per store
+// instruction (fp32: 4 bytes in -> float4 out; bf16: 8 -> 16; u8: 16 -> 16).  Needs Cout == C.
+// IDENT (u8 without gamma) skips the table: the kernel is then a flipping copy.
+template <typename T, int UNROLL, bool STATS, bool IDENT>
+__global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a, PlanarGeom g) {
+  constexpr int IB = 16 / (int)sizeof(T);
+  constexpr int LW = IB;  // one load per unit
   __shared__ T lut[kMaxC * 256];
-  build_lut<T>(a, lut);
+  if (!IDENT) build_lut<T>(a, lut);
   StatAcc acc;
   if (STATS) acc.clear();
   const uint32_t row_bytes = a.W * a.C;
-  const uint32_t upr = row_bytes / 16;
-  const uint64_t rows = (uint64_t)a.B * a.H;
-  const uint64_t total = rows * upr;
   T* dst = static_cast<T*>(a.dst);
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint32_t stride = gridDim.x * blockDim.x;
   const uint32_t C = a.C;
 
-  for (uint64_t u0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; u0 < total; u0 += stride * UNROLL) {
-    uint4 in[UNROLL];
+  for (uint32_t u0 = blockIdx.x * blockDim.x + threadIdx.x; u0 < g.total_units; u0 += stride * UNROLL) {
+    uint32_t in[UNROLL][IB / 4];
     uint64_t out_off[UNROLL];
     uint32_t phase[UNROLL];
     bool live[UNROLL];
 #pragma unroll
     for (int j = 0; j < UNROLL; ++j) {
-      uint64_t u = u0 + (uint64_t)j * stride;
-      live[j] = u < total;
+      const uint32_t u = u0 + j * stride;
+      live[j] = u < g.total_units && u >= u0;
       if (live[j]) {
-        uint64_t row = u / upr;
-        uint32_t ux = (uint32_t)(u - row * upr);
-        uint32_t b = (uint32_t)(row / a.H);
-        uint32_t y = (uint32_t)(row - (uint64_t)b * a.H);
-        uint32_t sy = a.flip ? a.H - 1 - y : y;
-        in[j] = ld_stream(reinterpret_cast<const uint4*>(
-            a.src + (uint64_t)b * a.src_image_stride + (uint64_t)sy * row_bytes + (uint64_t)ux * 16));
-        out_off[j] = row * row_bytes + (uint64_t)ux * 16;
-        phase[j] = (ux * 16u) % C;
+        const uint32_t row = fdiv(u, g.upr);
+        const uint32_t ux = u - row * g.upr.div;
+        const uint32_t b = fdiv(row, g.rows);
+        const uint32_t y = row - b * g.rows.div;
+        const uint32_t sy = a.flip ? a.H - 1 - y : y;
+        ld_words<LW>(a.src + (uint64_t)b * a.src_image_stride + (uint64_t)sy * row_bytes + (uint64_t)ux * IB, in[j]);
+        out_off[j] = (uint64_t)row * row_bytes + (uint64_t)ux * IB;
+        phase[j] = (ux * (uint32_t)IB) % C;
       }
     }
 #pragma unroll
     for (int j = 0; j < UNROLL; ++j) {
       if (!live[j]) continue;
-      const uint32_t* words = reinterpret_cast<const uint32_t*>(&in[j]);
-      T vals[16];
+      T vals[IB];
       uint32_t c = phase[j];
 #pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        vals[k] = lut[c * 256 + byte_of(words, k)];
+      for (int k = 0; k < IB; ++k) {
+        const uint32_t v = byte_of(in[j], k);
+        if constexpr (IDENT) vals[k] = OutT<T>::make((float)v, (uint8_t)v);
+        else vals[k] = lut[c * 256 + v];
         if (STATS) {
           float f = OutT<T>::as_float(vals[k]);
 #pragma unroll
@@ -320,7 +351,65 @@ __global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a) {
         }
         c = (c + 1 == C) ? 0 : c + 1;
       }
-      st_stream<T, 16>(dst + out_off[j], vals);
+      st_stream<T, IB>(dst + out_off[j], vals);
+    }
+  }
+  if (STATS) finish_stats(a, acc);
+}
+
+// ---- variant 2c: one pixel per thread (any width) -----------------------------------------------
+// For rows that are not a whole number of 16-byte units (odd widths): every thread takes one pixel
+// (a 32-bit load for C == 4, byte loads otherwise) and writes C_out scalars; lanes are consecutive
+// pixels, so planar stores are 128 contiguous bytes per warp instruction and loads are dense.
+template <typename T, int C, bool CHW, int UNROLL, bool STATS>
+__global__ void __launch_bounds__(kThreads) k1_pixel(K1Args a, PlanarGeom g) {
+  __shared__ T lut[kMaxC * 256];
+  build_lut<T>(a, lut);
+  StatAcc acc;
+  if (STATS) acc.clear();
+  const uint32_t plane = a.H * a.W;
+  T* dst = static_cast<T*>(a.dst);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t u0 = blockIdx.x * blockDim.x + threadIdx.x; u0 < g.total_units; u0 += stride * UNROLL) {
+    uint32_t px[UNROLL];
+    uint32_t bb[UNROLL], yy[UNROLL], xx[UNROLL];
+    bool live[UNROLL];
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      const uint32_t u = u0 + j * stride;
+      live[j] = u < g.total_units && u >= u0;
+      if (live[j]) {
+        const uint32_t row = fdiv(u, g.upr);   // upr = W here: units are pixels
+        const uint32_t x = u - row * g.upr.div;
+        const uint32_t b = fdiv(row, g.rows);
+        const uint32_t y = row - b * g.rows.div;
+        const uint32_t sy = a.flip ? a.H - 1 - y : y;
+        const uint8_t* sp = a.src + (uint64_t)b * a.src_image_stride + ((uint64_t)sy * a.W + x) * C;
+        if constexpr (C == 4) {
+          ld_words<4>(sp, &px[j]);
+        } else {
+          uint32_t w = 0;
+#pragma unroll
+          for (int c = 0; c < C; ++c) w |= (uint32_t)__ldg(sp + c) << (8 * c);
+          px[j] = w;
+        }
+        bb[j] = b; yy[j] = y; xx[j] = x;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      if (!live[j]) continue;
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        if (c < (int)a.Cout) {
+          const T o = lut[c * 256 + ((px[j] >> (8 * c)) & 0xffu)];
+          uint64_t off;
+          if (CHW) off = ((uint64_t)bb[j] * a.Cout + c) * plane + (uint64_t)yy[j] * a.W + xx[j];
+          else off = (((uint64_t)bb[j] * a.H + yy[j]) * a.W + xx[j]) * a.Cout + c;
+          dst[off] = o;
+          if (STATS) { float f = OutT<T>::as_float(o); acc.s[c] += f; acc.q[c] += (double)f * f; }
+        }
+      }
     }
   }
   if (STATS) finish_stats(a, acc);
@@ -348,6 +437,27 @@ int sm_count() {
   return cached;
 }
 
+FastDiv make_fastdiv(uint32_t d) {
+  // round-up method: q = (umulhi(n, m) + n) >> s, exact for n < 2^31
+  FastDiv f;
+  f.div = d;
+  uint32_t s = 0;
+  while ((1ull << s) < d) ++s;
+  f.shift = s;
+  f.mul = (uint32_t)((((1ull << s) - d) << 32) / d + 1);
+  return f;
+}
+
+bool planar_geom(const K1Args& a, int ppt, PlanarGeom& g) {
+  const uint64_t upr = a.W / ppt;
+  const uint64_t total = (uint64_t)a.B * a.H * upr;
+  if (total >= (1ull << 31) || (uint64_t)a.H * a.W >= (1ull << 30)) return false;
+  g.upr = make_fastdiv((uint32_t)upr);
+  g.rows = make_fastdiv(a.H);
+  g.total_units = (uint32_t)total;
+  return true;
+}
+
 template <typename T, bool STATS>
 int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStream_t st, int grid_cap) {
   const int sms = sm_count();
@@ -355,35 +465,91 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
   const bool aligned_src = (reinterpret_cast<uintptr_t>(a.src) % 16 == 0) && (a.src_image_stride % 16 == 0);
   const bool aligned_dst = reinterpret_cast<uintptr_t>(a.dst) % 16 == 0;
   const bool can_vec = aligned_src && aligned_dst && variant != 1;
+  const int tune_ctas = (p->reserved >> 8) & 0xff;
   auto grid_of = [&](uint64_t units, int unroll) {
-    int g = grid_for((units + unroll - 1) / unroll, sms, 8);
+    int g = grid_for((units + unroll - 1) / unroll, sms, tune_ctas ? tune_ctas : kDefaultCtasPerSm);
     if (grid_cap > 0 && g > grid_cap) g = grid_cap;
     return g;
   };
 #define LAUNCH_PLANAR(C_, PPT_, UNR_)                                                       \
   do {                                                                                      \
-    int g = grid_of(rows * (a.W / (PPT_)), (UNR_));                                         \
-    k1_planar<T, C_, PPT_, UNR_, STATS><<<g, kThreads, 0, st>>>(a);                         \
+    PlanarGeom geo;                                                                         \
+    if (!planar_geom(a, (PPT_), geo)) break; /* too many units for 32-bit indices */        \
+    int g = grid_of(geo.total_units, (UNR_));                                               \
+    k1_planar<T, C_, PPT_, UNR_, STATS><<<g, kThreads, 0, st>>>(a, geo);                    \
     g_last_variant = 2;                                                                     \
     return g;                                                                               \
   } while (0)
+  const int tune_unroll = p->reserved & 0xff;
   if (can_vec && p->chw && a.C == 4) {
     // widest unit whose stores are 16 bytes and that divides the row
     if (sizeof(T) == 1 && a.W % 16 == 0) LAUNCH_PLANAR(4, 16, 2);
     if (sizeof(T) == 2 && a.W % 8 == 0) LAUNCH_PLANAR(4, 8, 2);
-    if (a.W % 4 == 0) LAUNCH_PLANAR(4, 4, 4);
+    if (a.W % 4 == 0) {
+      if (!STATS && sizeof(T) == 4) {
+        if (tune_unroll == 1) LAUNCH_PLANAR(4, 4, 1);
+        if (tune_unroll == 2) LAUNCH_PLANAR(4, 4, 2);
+        if (tune_unroll == 8) LAUNCH_PLANAR(4, 4, 8);
+      }
+      LAUNCH_PLANAR(4, 4, 4);
+    }
   }
-  if (can_vec && p->chw && a.C == 3 && a.W % 16 == 0) LAUNCH_PLANAR(3, 16, 2);
+  if (can_vec && p->chw && a.C == 3) {
+    if (a.W % 16 == 0 && tune_unroll == 16) LAUNCH_PLANAR(3, 16, 2);
+    if (a.W % 8 == 0 && sizeof(T) <= 2) LAUNCH_PLANAR(3, 8, 2);
+    if (a.W % 4 == 0) LAUNCH_PLANAR(3, 4, 4);
+  }
+  if (can_vec && p->chw && a.C == 2 && a.W % 8 == 0) LAUNCH_PLANAR(2, 8, 4);
 #undef LAUNCH_PLANAR
-  if (can_vec && (!p->chw || a.C == 1) && a.Cout == a.C && (a.W * a.C) % 16 == 0 &&
-      (16 * sizeof(T)) % 16 == 0) {
-    int g = grid_of(rows * (a.W * a.C / 16), 4);
-    k1_interleaved<T, 4, STATS><<<g, kThreads, 0, st>>>(a);
-    g_last_variant = 2;
-    return g;
+  {
+    // interleaved output (or single-channel, where planar == interleaved)
+    constexpr uint32_t IB = 16 / sizeof(T);
+    const uint64_t row_bytes = (uint64_t)a.W * a.C;
+    if (can_vec && (!p->chw || a.C == 1) && a.Cout == a.C && row_bytes % IB == 0) {
+      PlanarGeom geo;
+      const uint64_t total = rows * (row_bytes / IB);
+      if (total < (1ull << 31)) {
+        geo.upr = make_fastdiv((uint32_t)(row_bytes / IB));
+        geo.rows = make_fastdiv(a.H);
+        geo.total_units = (uint32_t)total;
+        int g = grid_of(total, 4);
+        if (sizeof(T) == 1 && !a.use_gamma)
+          k1_interleaved<T, 4, STATS, true><<<g, kThreads, 0, st>>>(a, geo);
+        else
+          k1_interleaved<T, 4, STATS, false><<<g, kThreads, 0, st>>>(a, geo);
+        g_last_variant = 2;
+        return g;
+      }
+    }
   }
   if (variant == 2 || variant == 3)
-    return bt::fail(BT_E_INVALID, "requested vectorised variant needs 16-byte aligned rows (W=%u C=%u)", a.W, a.C);
+    return bt::fail(BT_E_INVALID, "requested vectorised variant needs rows made of whole 16-byte units (W=%u C=%u)", a.W, a.C);
+  if (variant != 1) {
+    // any width: one pixel per thread
+    PlanarGeom geo;
+    const uint64_t total = rows * a.W;
+    if (total < (1ull << 31) && (uint64_t)a.H * a.W < (1ull << 30)) {
+      geo.upr = make_fastdiv(a.W);
+      geo.rows = make_fastdiv(a.H);
+      geo.total_units = (uint32_t)total;
+      int g = grid_of(total, 4);
+#define LAUNCH_PIXEL(C_)                                                                          \
+  do {                                                                                            \
+    if (p->chw) k1_pixel<T, C_, true, 4, STATS><<<g, kThreads, 0, st>>>(a, geo);                  \
+    else k1_pixel<T, C_, false, 4, STATS><<<g, kThreads, 0, st>>>(a, geo);                        \
+  } while (0)
+      const bool px4 = a.C == 4 && reinterpret_cast<uintptr_t>(a.src) % 4 == 0 && a.src_image_stride % 4 == 0;
+      if (px4) LAUNCH_PIXEL(4);
+      else if (a.C == 3) LAUNCH_PIXEL(3);
+      else if (a.C == 2) LAUNCH_PIXEL(2);
+      else if (a.C == 1) LAUNCH_PIXEL(1);
+#undef LAUNCH_PIXEL
+      if (px4 || a.C < 4) {
+        g_last_variant = 4;
+        return g;
+      }
+    }
+  }
   {
     uint64_t total = rows * a.W * a.Cout;
     int g = grid_of(total, 1);

@@ -16,7 +16,7 @@ ESZ = {torch.float32: 4, torch.bfloat16: 2, torch.uint8: 1}
 
 
 def run(shape, dtype, layout="NCHW", stats=False, variant="auto", gamma=2.2, norm=True, streams=1, reps=200,
-        smooth=False):
+        smooth=False, tune=0):
     B, H, W, C = shape
     in_b = B * H * W * C
     out_b = in_b * ESZ[dtype]
@@ -30,7 +30,7 @@ def run(shape, dtype, layout="NCHW", stats=False, variant="auto", gamma=2.2, nor
         srcs = [torch.randint(0, 256, shape, dtype=torch.uint8, device=DEV, generator=g) for _ in range(rot)]
     oshape = (B, C, H, W) if layout == "NCHW" else (B, H, W, C)
     outs = [torch.empty(oshape, dtype=dtype, device=DEV) for _ in range(rot)]
-    kw = dict(flip=True, gamma=gamma, layout=layout, dtype=dtype, stats=stats, variant=variant)
+    kw = dict(flip=True, gamma=gamma, layout=layout, dtype=dtype, stats=stats, variant=variant, tune=tune)
     if norm and dtype != torch.uint8:
         kw.update(mean=127.5, std=127.5)
     spec = btt.Preprocess(**kw)
@@ -71,7 +71,7 @@ def run(shape, dtype, layout="NCHW", stats=False, variant="auto", gamma=2.2, nor
         e1.synchronize()
     us = e0.elapsed_time(e1) * 1e3 / (n * rot)
     return {"shape": list(shape), "dtype": str(dtype).split(".")[-1], "layout": layout, "stats": stats,
-            "variant": variant, "streams": streams, "smooth": smooth, "us": round(us, 2),
+            "variant": variant, "tune": hex(tune), "streams": streams, "smooth": smooth, "us": round(us, 2),
             "GBps": round((in_b + out_b) / us / 1e3, 1), "frac_meas": round((in_b + out_b) / us / 1e3 / 6548.5, 3)}
 
 
@@ -89,6 +89,19 @@ def main():
         dict(shape=C3, dtype=torch.float32), dict(shape=C5, dtype=torch.float32),
         dict(shape=(8, 480, 640, 3), dtype=torch.float32), dict(shape=(8, 481, 641, 4), dtype=torch.float32),
     ]
+    if len(sys.argv) > 1 and sys.argv[1] == "tune2":
+        cases = []
+        for shape in (C4, C3, C5, (16, 480, 640, 4), (32, 480, 640, 4)):
+            for unroll in (0, 8):
+                for ctas in (0, 32, 64, 128, 255):
+                    cases.append(dict(shape=shape, dtype=torch.float32, tune=unroll | (ctas << 8)))
+    elif len(sys.argv) > 1 and sys.argv[1] == "tune":
+        cases = []
+        for shape in (C2, C4):
+            for unroll in (0, 1, 2, 8):
+                for ctas in (0, 4, 6, 16, 32):
+                    cases.append(dict(shape=shape, dtype=torch.float32, tune=unroll | (ctas << 8)))
+        cases += [dict(shape=C2, dtype=torch.float32, tune=t, streams=4) for t in (0, 1, 2, 0x2001, 0x2002)]
     for c in cases:
         print(json.dumps(run(**c)), flush=True)
 
