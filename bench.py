@@ -54,7 +54,7 @@ def free_port():
     return p
 
 
-def spawn_publishers(module, n, transport="tcp", tag="p"):
+def spawn_publishers(module, n, transport="tcp", tag="p", extra=()):
     env = dict(os.environ)
     env["PYTHONPATH"] = os.pathsep.join([str(ROOT), str(PKG), env.get("PYTHONPATH", "")])
     addrs, procs = [], []
@@ -64,7 +64,7 @@ def spawn_publishers(module, n, transport="tcp", tag="p"):
         else:
             addr = "tcp://127.0.0.1:%d" % free_port()
         cmd = [sys.executable, "-m", module, "--bind", addr, "--btid", str(i), "--config", str(CONFIG),
-               "--height", str(H), "--width", str(W)]
+               "--height", str(H), "--width", str(W), *extra]
         procs.append(subprocess.Popen(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL))
         addrs.append(addr)
     return addrs, procs
@@ -81,6 +81,13 @@ def stop_publishers(procs):
             p.wait(timeout=5)
         except Exception:
             p.kill()
+    import glob
+    for p in procs:  # shared-memory segments of publishers that did not get to unlink them
+        for f in glob.glob("/dev/shm/btshm_%d_*" % p.pid):
+            try:
+                os.unlink(f)
+            except OSError:
+                pass
 
 
 class ClockSampler:
@@ -290,9 +297,10 @@ def large_batch_probe(torch, btt, dev, spec):
     return B2 * H2 * W2 * C * 5 / sec / 1e9, sec
 
 
-def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_threads=1):
+def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_threads=1, shm_slots=0):
     """Public API with host buffers: publishers -> DeviceLoader -> device batch (+ stats read back)."""
-    addrs, procs = spawn_publishers("blendtorch.btt.synthetic", PUBLISHERS, transport, tag="r%s" % os.environ.get("RANK", "0"))
+    addrs, procs = spawn_publishers("blendtorch.btt.synthetic", PUBLISHERS, transport, tag="r%s" % os.environ.get("RANK", "0"),
+                                    extra=("--shm-slots", str(shm_slots)) if shm_slots else ())
     try:
         total = (steps + warmup) * BATCH
         per_recv = -(-(steps + warmup) // receivers) * BATCH
@@ -391,6 +399,13 @@ def ours(args):
     e2e_sec = max_over_ranks(e2e_sec)
     images = sum_over_ranks(images)
     e2e_value = images / e2e_sec
+    # same leg over the opt-in shared-memory wire (payload by DMA from the producers' segments)
+    barrier()
+    shm_images, shm_sec, _, _ = e2e_leg(torch, btt, dev, args.steps, args.warmup, sampler, args.transport,
+                                        args.receivers, shm_slots=args.shm_slots)
+    barrier()
+    shm_sec = max_over_ranks(shm_sec)
+    shm_value = sum_over_ranks(shm_images) / shm_sec
     clocks = sampler.report()
 
     cpu = None
@@ -424,6 +439,11 @@ def ours(args):
             "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "gbs_h2d": e2e_value * h2d_bytes_img / 1e9 / world, "pcie_h2d_measured_gbs": h2d_gbs.value,
                     "frac_of_pcie_h2d": e2e_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value},
+            "e2e_shm_wire": {"value": shm_value, "unit": "images/s", "gbs_h2d": shm_value * h2d_bytes_img / 1e9 / world,
+                             "frac_of_pcie_h2d": shm_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value,
+                             "note": "opt-in wire for co-located producers (DataPublisher(shm_slots=%d)): payload goes "
+                                     "producer -> shared memory -> DMA, no consumer-side CPU copy; not the reference's "
+                                     "pickle wire, reported beside e2e, not instead of it" % args.shm_slots},
             "gpu_launches": args.steps, "gpu_launches_e2e": args.steps,
             "clocks": clocks,
             "cpu_baseline": cpu,
@@ -444,6 +464,7 @@ def main():
     ap.add_argument("--transport", default="tcp", choices=["tcp", "ipc"])
     ap.add_argument("--receivers", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shm-slots", type=int, default=32)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

@@ -63,7 +63,10 @@ typedef enum bt_kind {
   BT_KIND_BOOL = 3,    /* Python bool               -> collates to bool    */
   BT_KIND_NONE = 4,
   BT_KIND_STR = 5,     /* UTF-8 span in the message */
-  BT_KIND_OTHER = 6    /* parsed but not representable as a column */
+  BT_KIND_OTHER = 6,   /* parsed but not representable as a column */
+  BT_KIND_SHMREF = 7   /* ndarray announced by reference into a shared-memory segment (bt_shm_*):
+                          dtype/ndim/shape describe it, payload_off/len span the segment NAME inside
+                          the message, ival is the slot index */
 } bt_kind;
 
 #define BT_MAX_DIMS 8
@@ -156,6 +159,80 @@ int bt_ring_acquire(bt_ring* r, int* slot);
 int bt_ring_submit(bt_ring* r, int slot, void* dev_dst, uint64_t nbytes, void* stream);
 /* Block until the slot's last submitted copy is complete. */
 int bt_ring_wait(bt_ring* r, int slot);
+
+/* Ring-level ingest: bt_schema_ingest into slot `slot` of the ring, except that payloads announced
+ * by shared-memory reference (BT_KIND_SHMREF) are not copied by the CPU at all: they are remembered
+ * and bt_ring_submit_batch DMAs them from the (page-locked) segment straight into the device batch.
+ * The references are released back to their publisher once that copy has completed. */
+int bt_ring_ingest(bt_ring* r, int slot, const bt_schema* s, int item, const uint8_t* msg, uint64_t len);
+/* H2D of a filled slot holding `n_items` items: one cudaMemcpyAsync per column from the pinned slot,
+ * or one per item from shared memory for columns that arrived by reference; then the slot's event. */
+int bt_ring_submit_batch(bt_ring* r, int slot, const bt_schema* s, int n_items, void* dev_dst, void* stream);
+/* Copy the slot's pending shared-memory payloads into the pinned slot now and release them (used
+ * when a stream stalls with a partly filled batch, so that publishers never wait on a held slot). */
+int bt_ring_spill(bt_ring* r, int slot, const bt_schema* s);
+/* Non-blocking: release references of slots whose copies have completed. */
+int bt_ring_reap(bt_ring* r);
+
+/* ------------------------------------------------------------------------------------------
+ * Receive loop in C.
+ * Replaces the per-message Python of pkg_pytorch/blendtorch/btt/dataset.py:97-106 (poll, recv,
+ * pickle.loads, yield): one call fills a whole batch slot from a ZMQ PULL socket without the GIL.
+ * libzmq is not linked; the caller passes the entry points of the libzmq its binding already
+ * uses (pyzmq: ctypes.CDLL of its bundled libzmq) and the raw socket (`socket.underlying`).
+ * A receiver must only be used by the thread that owns the socket.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct bt_zmq_api {
+  void* msg_init;   /* int   zmq_msg_init(zmq_msg_t*)              */
+  void* msg_recv;   /* int   zmq_msg_recv(zmq_msg_t*, void*, int)  */
+  void* msg_data;   /* void* zmq_msg_data(zmq_msg_t*)              */
+  void* msg_size;   /* size_t zmq_msg_size(const zmq_msg_t*)       */
+  void* msg_close;  /* int   zmq_msg_close(zmq_msg_t*)             */
+  void* poll;       /* int   zmq_poll(zmq_pollitem_t*, int, long)  */
+  void* zmq_errno;  /* int   zmq_errno(void)                       */
+} bt_zmq_api;
+
+typedef struct bt_rx bt_rx;
+
+int bt_rx_create(const bt_zmq_api* api, void* zmq_socket, bt_rx** out);
+int bt_rx_destroy(bt_rx* rx);
+/* Wait up to timeout_ms for one message and hold it (BT_OK), or BT_E_TIMEOUT. */
+int bt_rx_recv(bt_rx* rx, int timeout_ms);
+/* The held message (valid until bt_rx_drop / the next fill). */
+int bt_rx_pending(bt_rx* rx, const uint8_t** data, uint64_t* len);
+int bt_rx_drop(bt_rx* rx);
+/* Receive and ingest (bt_ring_ingest) up to max_items messages into items first_item.. of `slot`.
+ * Returns BT_OK when max_items were placed; BT_E_TIMEOUT when no message arrived for slice_ms
+ * (call again); BT_E_UNSUPPORTED / BT_E_SCHEMA when a message needs the caller's pickle.loads
+ * path -- that message stays held (bt_rx_pending), the caller places it and calls bt_rx_drop.
+ * *n_done = messages placed by this call in every case. */
+int bt_rx_fill(bt_rx* rx, bt_ring* ring, int slot, const bt_schema* schema, int first_item, int max_items,
+               int slice_ms, int* n_done);
+/* Before closing the socket: take every message already queued on it (without waiting) and hand
+ * the shared-memory slots they reference back to their publishers, so that a consumer that stops
+ * early does not strand slots.  (Slots stranded anyway are reclaimed by the publisher after 30 s.) */
+int bt_rx_release_queued(bt_rx* rx, int* n_released);
+
+/* ------------------------------------------------------------------------------------------
+ * Shared-memory wire (opt-in, co-located producers).
+ * No counterpart in the reference, whose only transport is the pickled ZMQ message
+ * (btb/publisher.py:43).  A producer writes each large array into a slot of a POSIX shared-memory
+ * segment and sends, over the same ZMQ socket, the usual pickled dict with the array replaced by the
+ * tuple ("__btshm__", segment_name, slot, dtype_str, shape).  The consumer maps the segment once,
+ * page-locks it with cudaHostRegister, and copies slots to the device by DMA: zero CPU copies on the
+ * consumer side.  A slot is busy from bt_shm_acquire (producer) until bt_shm_release (consumer).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct bt_shm bt_shm;
+
+int bt_shm_create(const char* name, uint64_t slot_bytes, int nslots, bt_shm** out); /* producer */
+int bt_shm_attach(const char* name, int device, bt_shm** out); /* consumer; device >= 0 page-locks it */
+int bt_shm_close(bt_shm* s);                                    /* creator also unlinks the name */
+int bt_shm_nslots(const bt_shm* s);
+uint64_t bt_shm_slot_bytes(const bt_shm* s);
+void* bt_shm_slot_ptr(bt_shm* s, int slot);
+/* Producer: next slot in round-robin order once it is free; BT_E_TIMEOUT after timeout_ms (<0: forever). */
+int bt_shm_acquire(bt_shm* s, int timeout_ms, int* slot);
+int bt_shm_release(bt_shm* s, int slot);
 
 /* ------------------------------------------------------------------------------------------
  * K1: fused frame preprocessing on the device.

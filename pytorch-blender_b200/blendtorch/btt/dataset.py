@@ -17,6 +17,7 @@ import torch.utils.data as tud
 import zmq
 
 from .constants import DEFAULT_TIMEOUTMS
+from . import shm
 from .file import FileReader, FileRecorder
 
 
@@ -93,9 +94,13 @@ class RemoteIterableDataset(tud.IterableDataset):
                     ready = dict(poller.poll(self.timeoutms))
                     assert sock in ready, "No response within timeout interval."
                     data = sock.recv()
+                    obj = shm.resolve(pickle.loads(data))
                     if rec is not None:
+                        if shm.MARKER_BYTES in data[:4096]:
+                            # shared-memory wire: record the message with its payload in-line
+                            data = pickle.dumps(obj, protocol=3)
                         rec.save(data, is_pickled=True)
-                    yield self._item(pickle.loads(data))
+                    yield self._item(obj)
         finally:
             if sock is not None:
                 sock.close()

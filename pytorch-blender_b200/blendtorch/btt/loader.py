@@ -18,6 +18,7 @@ cost no kernel.  Ordering and delivery follow the reference: in order per publis
 receiver, unordered across receivers, every message delivered once
 (examples/datagen/Readme.md:172-177); back-pressure is the bounded queue + ZMQ high-water marks.
 """
+import pickle
 import queue
 import threading
 import ctypes as C
@@ -27,9 +28,11 @@ import torch
 import zmq
 
 from . import native as N
+from . import shm
 from .dataset import FileDataset, RemoteIterableDataset, open_pull_socket
 from .file import FileRecorder
 from .preprocess import Preprocess, preprocess_images
+from .rx import Receiver
 from .staging import Ring, Schema
 
 _DONE = object()
@@ -62,7 +65,7 @@ class _Stager:
         return self.ring.acquire()
 
     def ingest(self, slot, item, msg, host_rows):
-        self.schema.ingest(self.ring.ptr(slot), self.ring.view(slot), item, msg, host_rows)
+        self.ring.ingest(slot, self.schema, item, msg, host_rows)
 
     def finish(self, slot, n, host_rows):
         sch = self.schema
@@ -73,7 +76,7 @@ class _Stager:
         with torch.cuda.stream(self.stream):
             raw = torch.empty(max(used, 1), dtype=torch.uint8, device=self.device)
             if used:
-                self.ring.submit(slot, raw.data_ptr(), used, C.c_void_p(self.stream.cuda_stream))
+                self.ring.submit_batch(slot, sch, n, raw.data_ptr(), C.c_void_p(self.stream.cuda_stream))
             for c in sch.columns:
                 t = raw[c.slot_off:c.slot_off + n * c.item_bytes].view(_torch_dtype(c.dtype)).view((n,) + c.shape)
                 spec = self.specs.get(c.key)
@@ -196,59 +199,146 @@ class DeviceLoader:
             if ds.record_path_prefix is not None:
                 rec = FileRecorder(FileRecorder.filename(ds.record_path_prefix, rid), ds.max_items)
                 rec.__enter__()
-            custom = ds.has_custom_item()
-            slot, filled, host_rows = None, 0, {}
-            for _ in range(ds.max_items // self.num_receivers):
-                if stop.is_set():
-                    return
-                waited = 0
-                while True:  # poll in slices so that an abandoned iterator stops promptly
-                    step = min(100, max(ds.timeoutms - waited, 0))
-                    if sock in dict(poller.poll(step)):
-                        break
-                    waited += step
-                    if stop.is_set():
-                        return
-                    assert waited < ds.timeoutms, "No response within timeout interval."
-                frame = sock.recv(copy=False)
-                msg = frame.buffer
-                if rec is not None:
-                    rec.save(msg, is_pickled=True)
-                if custom:
-                    import pickle
-                    obj = ds._item(pickle.loads(msg))
-                    if stager is None:
-                        stager = _Stager(Schema.from_object(obj, self.batch_size), self.device,
-                                         self.ring_depth, self.specs, self.keep_raw)
-                    if slot is None:
-                        slot, filled, host_rows = stager.begin(), 0, {}
-                    stager.schema.ingest_object(stager.ring.view(slot), filled, obj, host_rows)
-                    self.stats["compat_items"] += 1
+            holder = []
+            try:
+                if rec is None and not ds.has_custom_item():
+                    self._stream_fast(ds, sock, out_q, stop, holder)
                 else:
-                    if stager is None:
-                        stager = self._new_stager(msg)
-                    if slot is None:
-                        slot, filled, host_rows = stager.begin(), 0, {}
-                    stager.ingest(slot, filled, msg, host_rows)
-                filled += 1
-                if filled == self.batch_size:
-                    if not self._emit(out_q, stop, stager, slot, filled, host_rows):
-                        return
-                    slot = None
-            if slot is not None and filled and not self.drop_last:
-                self._emit(out_q, stop, stager, slot, filled, host_rows)
+                    self._stream_compat(ds, sock, poller, rec, out_q, stop, holder)
+            finally:
+                stager = holder[0] if holder else None
         except BaseException as e:  # delivered to the consumer thread
             out_q.put(e)
         finally:
             if rec is not None:
                 rec.__exit__(None, None, None)
             if sock is not None:
+                try:  # do not strand shared-memory slots announced by messages we will never read
+                    tail = Receiver(sock)
+                    tail.release_queued()
+                    tail.close()
+                except Exception:
+                    pass
                 sock.close()
             ctx.term()
             if stager is not None:
                 self.stats["kernels"] += stager.kernels
                 stager.close()
             out_q.put(_DONE)
+
+    def _stream_fast(self, ds, sock, out_q, stop, holder):
+        """Batches filled by the C receive loop (bt_rx_fill): one call per batch, no GIL per message."""
+        rx = Receiver(sock)
+        try:
+            remaining = ds.max_items // self.num_receivers
+            waited = 0
+            # first message: defines the schema of the stream
+            while remaining > 0 and not rx.recv(100):
+                waited += 100
+                if stop.is_set():
+                    return
+                assert waited < ds.timeoutms, "No response within timeout interval."
+            if remaining <= 0:
+                return
+            stager = self._new_stager(rx.pending())
+            holder.append(stager)
+            ring, schema = stager.ring, stager.schema
+            while remaining > 0 and not stop.is_set():
+                slot, filled, host_rows = stager.begin(), 0, {}
+                want = min(self.batch_size, remaining)
+                waited = 0
+                while filled < want:
+                    if schema.native:
+                        rc, n = rx.fill(ring, slot, schema, filled, want - filled, 100)
+                    else:  # schema needs the pickle.loads decode for every message
+                        rc, n = (N.BT_E_UNSUPPORTED, 0) if rx.recv(100) else (N.BT_E_TIMEOUT, 0)
+                    filled += n
+                    if n:
+                        waited = 0
+                    if rc == N.BT_OK:
+                        break
+                    if rc == N.BT_E_TIMEOUT:
+                        waited += 100
+                        if stop.is_set():
+                            return
+                        # the stream stalled: do not sit on shared-memory slots of a partly filled
+                        # batch (their publishers may be waiting for exactly those slots)
+                        ring.spill(slot, schema)
+                        ring.reap()
+                        assert waited < ds.timeoutms, "No response within timeout interval."
+                        continue
+                    # this message is outside the native subset: the reference's own decode, same slot
+                    stager.schema.ingest_object(ring.view(slot), filled, shm.resolve(pickle.loads(rx.pending())), host_rows)
+                    rx.drop()
+                    self.stats["compat_items"] += 1
+                    filled += 1
+                    waited = 0
+                remaining -= filled
+                if filled < self.batch_size and self.drop_last:
+                    break
+                if not self._emit(out_q, stop, stager, slot, filled, host_rows):
+                    return
+        finally:
+            rx.close()
+
+    def _stream_compat(self, ds, sock, poller, rec, out_q, stop, holder):
+        """Per-message Python loop: needed when every message has to pass through Python anyway
+        (a user item_transform / overridden _item, or the recording tee)."""
+        stager = None
+        custom = ds.has_custom_item()
+        slot, filled, host_rows = None, 0, {}
+        for _ in range(ds.max_items // self.num_receivers):
+            if stop.is_set():
+                return
+            waited = 0
+            while True:  # poll in slices so that an abandoned iterator stops promptly
+                step = min(100, max(ds.timeoutms - waited, 0))
+                if sock in dict(poller.poll(step)):
+                    break
+                waited += step
+                if stop.is_set():
+                    return
+                if stager is not None:
+                    # the stream stalled: do not sit on shared-memory slots of a partly filled
+                    # batch (their publishers may be waiting for exactly those slots)
+                    if slot is not None:
+                        stager.ring.spill(slot, stager.schema)
+                    stager.ring.reap()
+                assert waited < ds.timeoutms, "No response within timeout interval."
+            frame = sock.recv(copy=False)
+            msg = frame.buffer
+            if stager is not None:
+                stager.ring.reap()
+            by_ref = shm.MARKER_BYTES in bytes(msg[:4096]) if (rec is not None or custom) else False
+            if rec is not None and not by_ref:
+                rec.save(msg, is_pickled=True)
+            if custom or (rec is not None and by_ref):
+                obj = shm.resolve(pickle.loads(msg))
+                if rec is not None and by_ref:
+                    # recordings must be self-contained: store the message with its payload in-line
+                    rec.save(pickle.dumps(obj, protocol=3), is_pickled=True)
+                obj = ds._item(obj)
+                if stager is None:
+                    stager = _Stager(Schema.from_object(obj, self.batch_size), self.device,
+                                     self.ring_depth, self.specs, self.keep_raw)
+                if slot is None:
+                    slot, filled, host_rows = stager.begin(), 0, {}
+                stager.schema.ingest_object(stager.ring.view(slot), filled, obj, host_rows)
+                self.stats["compat_items"] += 1
+            else:
+                if stager is None:
+                    stager = self._new_stager(msg)
+                    holder.append(stager)
+                if slot is None:
+                    slot, filled, host_rows = stager.begin(), 0, {}
+                stager.ingest(slot, filled, msg, host_rows)
+            filled += 1
+            if filled == self.batch_size:
+                if not self._emit(out_q, stop, stager, slot, filled, host_rows):
+                    return
+                slot = None
+        if slot is not None and filled and not self.drop_last:
+            self._emit(out_q, stop, stager, slot, filled, host_rows)
 
     def _replay_order(self):
         n = len(self.dataset)

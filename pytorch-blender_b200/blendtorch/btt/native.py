@@ -17,7 +17,7 @@ BT_E_CUDA, BT_E_NOMEM, BT_E_IO, BT_E_TIMEOUT, BT_E_TOO_LARGE = -5, -6, -7, -8, -
 (BT_U8, BT_I8, BT_U16, BT_I16, BT_U32, BT_I32, BT_U64, BT_I64,
  BT_F16, BT_F32, BT_F64, BT_BOOL, BT_BF16) = range(13)
 (BT_KIND_NDARRAY, BT_KIND_INT, BT_KIND_FLOAT, BT_KIND_BOOL,
- BT_KIND_NONE, BT_KIND_STR, BT_KIND_OTHER) = range(7)
+ BT_KIND_NONE, BT_KIND_STR, BT_KIND_OTHER, BT_KIND_SHMREF) = range(8)
 
 BT_MAX_DIMS = 8
 BT_MAX_KEY = 64
@@ -97,6 +97,25 @@ def _load():
         "bt_ring_acquire": (i32, [vp, C.POINTER(i32)]),
         "bt_ring_submit": (i32, [vp, i32, vp, u64, vp]),
         "bt_ring_wait": (i32, [vp, i32]),
+        "bt_ring_ingest": (i32, [vp, i32, vp, i32, vp, u64]),
+        "bt_ring_submit_batch": (i32, [vp, i32, vp, i32, vp, vp]),
+        "bt_ring_spill": (i32, [vp, i32, vp]),
+        "bt_ring_reap": (i32, [vp]),
+        "bt_rx_create": (i32, [vp, vp, C.POINTER(vp)]),
+        "bt_rx_destroy": (i32, [vp]),
+        "bt_rx_recv": (i32, [vp, i32]),
+        "bt_rx_pending": (i32, [vp, C.POINTER(vp), C.POINTER(u64)]),
+        "bt_rx_drop": (i32, [vp]),
+        "bt_rx_fill": (i32, [vp, vp, i32, vp, i32, i32, i32, C.POINTER(i32)]),
+        "bt_rx_release_queued": (i32, [vp, C.POINTER(i32)]),
+        "bt_shm_create": (i32, [C.c_char_p, u64, i32, C.POINTER(vp)]),
+        "bt_shm_attach": (i32, [C.c_char_p, i32, C.POINTER(vp)]),
+        "bt_shm_close": (i32, [vp]),
+        "bt_shm_nslots": (i32, [vp]),
+        "bt_shm_slot_bytes": (u64, [vp]),
+        "bt_shm_slot_ptr": (vp, [vp, i32]),
+        "bt_shm_acquire": (i32, [vp, i32, C.POINTER(i32)]),
+        "bt_shm_release": (i32, [vp, i32]),
         "bt_build_gamma_lut": (i32, [C.c_double, C.POINTER(C.c_uint8 * 256)]),
         "bt_preprocess_scratch_bytes": (u64, [C.POINTER(PreprocessParams)]),
         "bt_preprocess_launch": (i32, [C.POINTER(PreprocessParams), vp]),
@@ -119,6 +138,11 @@ EXPORTS = ["bt_last_error", "bt_abi_version", "bt_scan_message", "bt_schema_crea
            "bt_schema_num_columns", "bt_schema_column", "bt_schema_slot_bytes", "bt_schema_ingest",
            "bt_schema_ingest_many", "bt_ring_create", "bt_ring_destroy", "bt_ring_depth",
            "bt_ring_slot_bytes", "bt_ring_slot_ptr", "bt_ring_acquire", "bt_ring_submit", "bt_ring_wait",
+           "bt_ring_ingest", "bt_ring_submit_batch", "bt_ring_spill", "bt_ring_reap",
+           "bt_rx_create", "bt_rx_destroy", "bt_rx_recv", "bt_rx_pending", "bt_rx_drop", "bt_rx_fill",
+           "bt_rx_release_queued",
+           "bt_shm_create", "bt_shm_attach", "bt_shm_close", "bt_shm_nslots", "bt_shm_slot_bytes",
+           "bt_shm_slot_ptr", "bt_shm_acquire", "bt_shm_release",
            "bt_build_gamma_lut", "bt_preprocess_scratch_bytes", "bt_preprocess_launch",
            "bt_preprocess_last_variant", "bt_preprocess_stats_static", "bt_project_launch", "bt_device_count", "bt_measure_h2d"]
 

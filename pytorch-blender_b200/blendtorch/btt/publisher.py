@@ -5,9 +5,14 @@ Same class name, constructor and ``publish(**kwargs)`` contract as the reference
 a bounded send queue that blocks the caller when consumers are slow, and messages that are
 ``pickle({'btid': btid, **kwargs})``.  It exists on the btt side so that synthetic producers
 (tests, benchmarks, simulators that are not Blender) speak the exact wire format.
+
+Opt-in extension for producers on the same host as their consumers: ``shm_slots=N`` sends every
+array of at least ``shm_threshold`` bytes through a shared-memory segment and only a reference
+through ZMQ (see shm.py).  Such messages are understood by this package, not by the reference.
 """
 import pickle
 
+import numpy as np
 import zmq
 
 
@@ -19,9 +24,14 @@ class DataPublisher:
     send_hwm: send queue size before `publish` blocks.
     lingerms: how long unsent messages survive `close`.
     protocol: pickle protocol; None = pyzmq's default, 3 = what Blender's Python 3.7 emits.
+    shm_slots: 0 = reference wire (everything pickled in-line); N > 0 = shared-memory wire with N
+        slots (the segment is created on the first large array and sized for it).
+    shm_threshold: smallest array, in bytes, that goes through shared memory.
+    shm_timeoutms: how long `publish` waits for a free slot before raising (consumers gone).
     """
 
-    def __init__(self, bind_address, btid=None, send_hwm=10, lingerms=0, protocol=None):
+    def __init__(self, bind_address, btid=None, send_hwm=10, lingerms=0, protocol=None,
+                 shm_slots=0, shm_threshold=65536, shm_timeoutms=10000):
         self.ctx = zmq.Context()
         self.sock = self.ctx.socket(zmq.PUSH)
         self.sock.setsockopt(zmq.SNDHWM, send_hwm)
@@ -29,11 +39,27 @@ class DataPublisher:
         self.sock.setsockopt(zmq.IMMEDIATE, 1)
         self.sock.bind(bind_address)
         self.btid = btid
+        self.lingerms = lingerms
         self.protocol = pickle.DEFAULT_PROTOCOL if protocol is None else protocol  # == pyzmq default
+        self.shm_slots, self.shm_threshold, self.shm_timeoutms = int(shm_slots), int(shm_threshold), int(shm_timeoutms)
+        self._segment = None
+
+    def _by_reference(self, array):
+        from . import shm
+        if self._segment is None:
+            self._segment = shm.Segment(array.nbytes, self.shm_slots)
+        if array.nbytes > self._segment.slot_bytes:
+            return array  # does not fit the segment sized by the first frame: send it in-line
+        return self._segment.put(array, self.shm_timeoutms)
 
     def publish(self, **kwargs):
         """Send one message; `btid` is added implicitly."""
-        self.publish_raw(pickle.dumps({"btid": self.btid, **kwargs}, protocol=self.protocol))
+        data = {"btid": self.btid, **kwargs}
+        if self.shm_slots > 0:
+            for k, v in data.items():
+                if isinstance(v, np.ndarray) and v.nbytes >= self.shm_threshold and not v.dtype.hasobject:
+                    data[k] = self._by_reference(v)
+        self.publish_raw(pickle.dumps(data, protocol=self.protocol))
 
     def publish_raw(self, data, copy=True):
         """Send an already pickled message (replaying recordings, pre-pickled synthetic frames)."""
@@ -42,6 +68,11 @@ class DataPublisher:
     def close(self):
         self.sock.close()
         self.ctx.term()
+        if self._segment is not None:
+            if self.lingerms > 0:
+                self._segment.drain(self.lingerms)  # let consumers finish with the slots they hold
+            self._segment.close()
+            self._segment = None
 
     def __enter__(self):
         return self

@@ -1,0 +1,106 @@
+"""Shared-memory wire (opt-in): payloads travel through a POSIX shared-memory segment, the ZMQ
+message only carries a reference.  No counterpart in the reference (its only transport is the
+pickled ZMQ message, btb/publisher.py:43); see include/bt_b200.h `bt_shm_*`.
+
+A message on this wire is the usual pickled dict in which a large array is replaced by
+
+    ("__btshm__", segment_name, slot, dtype_str, shape)
+
+Both ends must opt in: the producer with ``DataPublisher(..., shm_slots=N)``, the consumer by being
+this package (``DeviceLoader`` DMAs the slot straight to the GPU; host iteration copies it out).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import native as N
+
+MARKER = "__btshm__"
+MARKER_BYTES = b"__btshm__"
+
+
+def is_marker(v):
+    return isinstance(v, tuple) and len(v) == 5 and v[0] == MARKER
+
+
+class Segment:
+    """Producer side: a segment of `nslots` slots of `slot_bytes` each."""
+
+    def __init__(self, slot_bytes, nslots, name=None):
+        self.name = name or "/btshm_%d_%x" % (os.getpid(), int.from_bytes(os.urandom(4), "little"))
+        self.handle = C.c_void_p()
+        N.check(N.lib.bt_shm_create(self.name.encode(), int(slot_bytes), int(nslots), C.byref(self.handle)))
+        self.nslots = nslots
+        self.slot_bytes = N.lib.bt_shm_slot_bytes(self.handle)
+        self._views = []
+        for i in range(nslots):
+            p = N.lib.bt_shm_slot_ptr(self.handle, i)
+            self._views.append(np.frombuffer((C.c_uint8 * self.slot_bytes).from_address(p), dtype=np.uint8))
+
+    def acquire(self, timeout_ms=10000):
+        s = C.c_int()
+        N.check(N.lib.bt_shm_acquire(self.handle, int(timeout_ms), C.byref(s)))
+        return s.value
+
+    def view(self, slot):
+        return self._views[slot]
+
+    def put(self, array, timeout_ms=10000):
+        """Copy `array` into the next free slot and return the marker that announces it."""
+        a = np.ascontiguousarray(array)
+        if a.nbytes > self.slot_bytes:
+            raise ValueError("array of %d bytes does not fit a %d-byte slot" % (a.nbytes, self.slot_bytes))
+        slot = self.acquire(timeout_ms)
+        self._views[slot][:a.nbytes] = a.reshape(-1).view(np.uint8)
+        return (MARKER, self.name, slot, a.dtype.str, tuple(a.shape))
+
+    def drain(self, timeout_ms):
+        """Wait (up to `timeout_ms` per slot) until consumers have released every slot."""
+        try:
+            for _ in range(self.nslots):
+                N.check(N.lib.bt_shm_release(self.handle, self.acquire(timeout_ms)))
+        except N.NativeError:
+            pass
+
+    def close(self):
+        if self.handle:
+            self._views = []
+            N.lib.bt_shm_close(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_attached = {}
+
+
+def fetch(marker):
+    """Consumer side without a GPU in the loop: copy the announced array out and free its slot."""
+    _, name, slot, dtype_str, shape = marker
+    h = _attached.get(name)
+    if h is None:
+        h = C.c_void_p()
+        N.check(N.lib.bt_shm_attach(name.encode(), -1, C.byref(h)))
+        _attached[name] = h
+    dt = np.dtype(dtype_str)
+    n = int(np.prod(shape, dtype=np.int64)) * dt.itemsize
+    p = N.lib.bt_shm_slot_ptr(h, int(slot))
+    if not p or n > N.lib.bt_shm_slot_bytes(h):
+        raise N.NativeError(N.BT_E_INVALID, "shared-memory reference out of range")
+    out = np.frombuffer((C.c_uint8 * n).from_address(p), dtype=np.uint8).copy().view(dt).reshape(shape)
+    N.check(N.lib.bt_shm_release(h, int(slot)))
+    return out
+
+
+def resolve(obj):
+    """Replace every marker in a received message dict by the array it announces."""
+    if isinstance(obj, dict):
+        for k, v in obj.items():
+            if is_marker(v):
+                obj[k] = fetch(v)
+    return obj

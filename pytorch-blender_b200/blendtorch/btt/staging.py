@@ -19,6 +19,7 @@ import pickle
 import numpy as np
 
 from . import native as N
+from . import shm
 
 _ALIGN = 256
 
@@ -71,7 +72,7 @@ class Schema:
             return cls(batch, cols, handle=h)
         if rc not in (N.BT_E_UNSUPPORTED,):
             N.check(rc)
-        return cls.from_object(pickle.loads(msg), batch)
+        return cls.from_object(shm.resolve(pickle.loads(msg)), batch)
 
     @classmethod
     def from_object(cls, obj, batch):
@@ -129,7 +130,7 @@ class Schema:
                 return
             if rc not in (N.BT_E_UNSUPPORTED, N.BT_E_SCHEMA):
                 N.check(rc)
-        self.ingest_object(slot_view, item, pickle.loads(msg), host_rows)
+        self.ingest_object(slot_view, item, shm.resolve(pickle.loads(msg)), host_rows)
 
     def ingest_object(self, slot_view, item, obj, host_rows=None):
         for c in self.columns:
@@ -194,6 +195,37 @@ class Ring:
 
     def submit(self, slot, dev_ptr, nbytes, stream_handle):
         N.check(N.lib.bt_ring_submit(self.handle, slot, dev_ptr, nbytes, stream_handle))
+
+    def ingest(self, slot, schema, item, msg, host_rows=None):
+        """Place message `msg` as item `item` of `slot`.  Payloads carried in-line are copied once
+        into the pinned slot; payloads announced by shared-memory reference are only noted and go
+        to the GPU by DMA in `submit_batch`."""
+        if schema.handle is not None:
+            addr, n = N.buffer_address(msg)
+            rc = N.lib.bt_ring_ingest(self.handle, slot, schema.handle, item, addr, n)
+            if rc == N.BT_OK:
+                return
+            if rc not in (N.BT_E_UNSUPPORTED, N.BT_E_SCHEMA):
+                N.check(rc)
+        schema.ingest_object(self._views[slot], item, shm.resolve(pickle.loads(msg)), host_rows)
+
+    def submit_batch(self, slot, schema, n_items, dev_ptr, stream_handle):
+        """H2D of a filled slot: per column from pinned memory, per item from shared memory."""
+        if schema.handle is not None:
+            N.check(N.lib.bt_ring_submit_batch(self.handle, slot, schema.handle, n_items, dev_ptr, stream_handle))
+        else:
+            used = 0
+            for c in schema.columns:
+                used = max(used, c.slot_off + n_items * c.item_bytes)
+            if used:
+                self.submit(slot, dev_ptr, used, stream_handle)
+
+    def spill(self, slot, schema):
+        if schema.handle is not None:
+            N.check(N.lib.bt_ring_spill(self.handle, slot, schema.handle))
+
+    def reap(self):
+        N.check(N.lib.bt_ring_reap(self.handle))
 
     def wait(self, slot):
         N.check(N.lib.bt_ring_wait(self.handle, slot))

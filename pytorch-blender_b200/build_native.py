@@ -18,7 +18,7 @@ ROOT = HERE.parent
 CSRC = HERE / "csrc"
 OUT_DIR = HERE / "blendtorch" / "btt" / "_native"
 LIB = OUT_DIR / "libbt_b200.so"
-SOURCES = ["scan.cpp", "ring.cu", "preprocess.cu", "project.cu"]
+SOURCES = ["scan.cpp", "rx.cpp", "ring.cu", "shm.cu", "preprocess.cu", "project.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 
@@ -48,7 +48,7 @@ def build(force=False, verbose=False):
     cmd = [_nvcc(), *ARCH, "-O3", "-std=c++17", "-lineinfo", "--threads", "4",
            "-Xcompiler", "-fPIC,-O3,-Wall", "-shared",
            "-I", str(ROOT / "include"), "-I", str(CSRC),
-           "-o", str(LIB), *srcs, "-lpthread"]
+           "-o", str(LIB), *srcs, "-lpthread", "-lrt"]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))

@@ -41,3 +41,38 @@ inline int dtype_size(int dt) {
       return bt::fail(BT_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
                       __FILE__, __LINE__);                                             \
   } while (0)
+
+// ---- internals shared between scan.cpp, ring.cu and shm.cu --------------------------------------
+#include <vector>
+
+struct bt_schema {
+  std::vector<bt_column> cols;
+  int batch = 0;
+  uint64_t slot_bytes = 0;
+};
+
+namespace bt {
+
+// One payload that was announced by reference (shared-memory wire) instead of carried in-line.
+struct PendingRef {
+  bt_shm* seg;
+  int shm_slot;
+  int column;
+  int item;
+  uint64_t nbytes;
+};
+
+int scan_fields(const uint8_t* msg, uint64_t len, std::vector<bt_field>& out);
+uint64_t field_bytes(const bt_field& f);
+std::vector<bt_field>& tls_fields();
+
+// Copy the scanned fields of one message into item `item` of the slot at `base`.  Fields that
+// arrive as shared-memory references are appended to `refs` when it is non-null (the caller will
+// DMA them straight from the segment), otherwise they are copied and released here.
+int place_fields(const bt_schema* s, uint8_t* base, int item, const uint8_t* msg,
+                 const std::vector<bt_field>& f, std::vector<PendingRef>* refs, int device);
+
+// Process-wide registry of attached segments (shm.cu).
+int shm_attach_cached(const char* name, size_t name_len, int device, bt_shm** out);
+
+}  // namespace bt

@@ -23,7 +23,17 @@ struct bt_ring {
   std::vector<cudaEvent_t> done;
   std::vector<uint8_t> in_flight;
   int next = 0;
+  // shared-memory wire: payloads announced by reference
+  std::vector<std::vector<bt::PendingRef>> pending;   // ingested, copy not yet issued
+  std::vector<std::vector<bt::PendingRef>> copying;   // DMA issued, released when the event completes
 };
+
+namespace {
+void release_refs(std::vector<bt::PendingRef>& v) {
+  for (const bt::PendingRef& r : v) bt_shm_release(r.seg, r.shm_slot);
+  v.clear();
+}
+}  // namespace
 
 extern "C" {
 
@@ -35,6 +45,8 @@ int bt_ring_create(int device, uint64_t slot_bytes, int depth, bt_ring** out) {
   r->slot_bytes = bt::align_up(slot_bytes, 4096);
   r->depth = depth;
   r->in_flight.assign(depth, 0);
+  r->pending.resize(depth);
+  r->copying.resize(depth);
   if (device >= 0) {
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess)
@@ -75,6 +87,8 @@ int bt_ring_destroy(bt_ring* r) {
     for (int i = 0; i < r->depth; ++i) {
       if (r->in_flight[i]) cudaEventSynchronize(r->done[i]);
       cudaEventDestroy(r->done[i]);
+      release_refs(r->copying[i]);
+      release_refs(r->pending[i]);
     }
     cudaFreeHost(r->base);
   } else {
@@ -101,6 +115,7 @@ int bt_ring_wait(bt_ring* r, int slot) {
     BT_CUDA_TRY(cudaEventSynchronize(r->done[slot]));
     r->in_flight[slot] = 0;
   }
+  release_refs(r->copying[slot]);
   return BT_OK;
 }
 
@@ -122,6 +137,87 @@ int bt_ring_submit(bt_ring* r, int slot, void* dev_dst, uint64_t nbytes, void* s
   BT_CUDA_TRY(cudaMemcpyAsync(dev_dst, r->base + r->slot_bytes * (uint64_t)slot, nbytes, cudaMemcpyHostToDevice, st));
   BT_CUDA_TRY(cudaEventRecord(r->done[slot], st));
   r->in_flight[slot] = 1;
+  return BT_OK;
+}
+
+int bt_ring_ingest(bt_ring* r, int slot, const bt_schema* s, int item, const uint8_t* msg, uint64_t len) {
+  if (!r || !s || slot < 0 || slot >= r->depth || item < 0 || item >= s->batch || s->slot_bytes > r->slot_bytes)
+    return bt::fail(BT_E_INVALID, "bt_ring_ingest: bad arguments");
+  std::vector<bt_field>& f = bt::tls_fields();
+  int rc = bt::scan_fields(msg, len, f);
+  if (rc != BT_OK) return rc;
+  const size_t before = r->pending[slot].size();
+  rc = bt::place_fields(s, r->base + r->slot_bytes * (uint64_t)slot, item, msg, f,
+                        r->pinned ? &r->pending[slot] : nullptr, r->device);
+  if (rc != BT_OK) {
+    // Forget (but do not release) what a rejected message referenced: the caller's compatibility
+    // decode fetches those payloads itself and releases them.
+    r->pending[slot].resize(before);
+  }
+  return rc;
+}
+
+int bt_ring_spill(bt_ring* r, int slot, const bt_schema* s) {
+  if (!r || !s || slot < 0 || slot >= r->depth) return bt::fail(BT_E_INVALID, "bt_ring_spill: bad arguments");
+  uint8_t* base = r->base + r->slot_bytes * (uint64_t)slot;
+  for (const bt::PendingRef& p : r->pending[slot]) {
+    const bt_column& c = s->cols[p.column];
+    memcpy(base + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot), p.nbytes);
+  }
+  release_refs(r->pending[slot]);
+  return BT_OK;
+}
+
+int bt_ring_submit_batch(bt_ring* r, int slot, const bt_schema* s, int n_items, void* dev_dst, void* stream) {
+  if (!r || !s || slot < 0 || slot >= r->depth || !dev_dst || n_items < 0 || n_items > s->batch)
+    return bt::fail(BT_E_INVALID, "bt_ring_submit_batch: bad arguments");
+  if (!r->pinned) return bt::fail(BT_E_CUDA, "ring was created without a CUDA device; nothing to copy to");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint8_t* host = r->base + r->slot_bytes * (uint64_t)slot;
+  uint8_t* dev = static_cast<uint8_t*>(dev_dst);
+  std::vector<bt::PendingRef>& pend = r->pending[slot];
+  // how many items of each column arrived by reference
+  std::vector<int> by_ref(s->cols.size(), 0);
+  for (const bt::PendingRef& p : pend) by_ref[p.column]++;
+  for (size_t ci = 0; ci < s->cols.size(); ++ci) {
+    const bt_column& c = s->cols[ci];
+    if (by_ref[ci] == n_items && n_items > 0) continue;          // whole column comes from shared memory
+    if (by_ref[ci] > 0) {                                        // mixed: bring the referenced items in first
+      for (const bt::PendingRef& p : pend)
+        if (p.column == (int)ci)
+          memcpy(host + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot), p.nbytes);
+    }
+    const uint64_t nbytes = c.item_bytes * (uint64_t)n_items;
+    if (nbytes)
+      BT_CUDA_TRY(cudaMemcpyAsync(dev + c.slot_off, host + c.slot_off, nbytes, cudaMemcpyHostToDevice, st));
+  }
+  std::vector<bt::PendingRef>& fly = r->copying[slot];
+  for (const bt::PendingRef& p : pend) {
+    const bt_column& c = s->cols[p.column];
+    if (by_ref[p.column] == n_items)
+      BT_CUDA_TRY(cudaMemcpyAsync(dev + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot),
+                                  p.nbytes, cudaMemcpyHostToDevice, st));
+    fly.push_back(p);   // (mixed columns were copied above; their slots are released with the rest)
+  }
+  pend.clear();
+  BT_CUDA_TRY(cudaEventRecord(r->done[slot], st));
+  r->in_flight[slot] = 1;
+  return BT_OK;
+}
+
+int bt_ring_reap(bt_ring* r) {
+  if (!r) return bt::fail(BT_E_INVALID, "null ring");
+  if (!r->pinned) return BT_OK;
+  for (int i = 0; i < r->depth; ++i) {
+    if (!r->in_flight[i] || r->copying[i].empty()) continue;
+    cudaError_t e = cudaEventQuery(r->done[i]);
+    if (e == cudaSuccess) {
+      r->in_flight[i] = 0;
+      release_refs(r->copying[i]);
+    } else if (e != cudaErrorNotReady) {
+      return bt::fail(BT_E_CUDA, "cudaEventQuery failed: %s", cudaGetErrorString(e));
+    }
+  }
   return BT_OK;
 }
 

@@ -363,6 +363,35 @@ void classify(const Scanner& s, int idx, bt_field* f) {
     case N_INT: f->kind = BT_KIND_INT; f->ival = v.i; return;
     case N_FLOAT: f->kind = BT_KIND_FLOAT; f->fval = v.f; return;
     case N_STR: f->kind = BT_KIND_STR; f->payload_off = v.off; f->payload_len = v.len; return;
+    case N_TUPLE: {
+      // shared-memory wire marker: ("__btshm__", segment_name, slot, dtype_str, shape)
+      const std::vector<int>& t = s.kidpool[v.kids];
+      if (t.size() != 5) return;
+      const Node& tag = s.nodes[t[0]];
+      if (tag.k != N_STR || !s.span_eq(tag.off, tag.len, "__btshm__")) return;
+      const Node& name = s.nodes[t[1]];
+      const Node& slot = s.nodes[t[2]];
+      const Node& dts = s.nodes[t[3]];
+      if (name.k != N_STR || name.len == 0 || name.len >= BT_MAX_KEY || slot.k != N_INT || slot.i < 0) return;
+      if (dts.k != N_STR || dts.len != 3) return;  // numpy dtype.str: '<f4', '|u1'
+      const char e = (char)s.p[dts.off], c0 = (char)s.p[dts.off + 1];
+      const int size = (char)s.p[dts.off + 2] - '0';
+      if (e == '>' && size > 1) return;
+      int dt = -1;
+      switch (c0) {
+        case 'u': dt = size == 1 ? BT_U8 : size == 2 ? BT_U16 : size == 4 ? BT_U32 : size == 8 ? BT_U64 : -1; break;
+        case 'i': dt = size == 1 ? BT_I8 : size == 2 ? BT_I16 : size == 4 ? BT_I32 : size == 8 ? BT_I64 : -1; break;
+        case 'f': dt = size == 2 ? BT_F16 : size == 4 ? BT_F32 : size == 8 ? BT_F64 : -1; break;
+        case 'b': dt = size == 1 ? BT_BOOL : -1; break;
+      }
+      if (dt < 0 || !parse_shape(s, t[4], f)) return;
+      f->kind = BT_KIND_SHMREF;
+      f->dtype = dt;
+      f->payload_off = name.off;   // span of the segment name
+      f->payload_len = name.len;
+      f->ival = slot.i;
+      return;
+    }
     case N_OBJ: break;
     default: return;
   }
@@ -415,6 +444,8 @@ Scanner& tls_scanner() {
   return s;
 }
 
+}  // namespace
+
 // Scan into the thread-local scanner and describe top-level dict entries.
 int scan_fields(const uint8_t* msg, uint64_t len, std::vector<bt_field>& out) {
   if (!msg && len) return fail(BT_E_INVALID, "null message");
@@ -447,16 +478,77 @@ std::vector<bt_field>& tls_fields() {
   return v;
 }
 
-}  // namespace
+uint64_t field_bytes(const bt_field& f) {
+  uint64_t count = 1;
+  for (int i = 0; i < f.ndim; ++i) count *= (uint64_t)f.shape[i];
+  return count * (uint64_t)dtype_size(f.dtype);
+}
+
+int place_fields(const bt_schema* s, uint8_t* base, int item, const uint8_t* msg,
+                 const std::vector<bt_field>& f, std::vector<PendingRef>* refs, int device) {
+  if (f.size() != s->cols.size())
+    return fail(BT_E_SCHEMA, "message has %zu fields, schema has %zu", f.size(), s->cols.size());
+  for (size_t ci = 0; ci < s->cols.size(); ++ci) {
+    const bt_column& c = s->cols[ci];
+    const bt_field* fi = &f[ci];
+    if (strcmp(fi->key, c.key) != 0) {  // same keys in another order
+      fi = nullptr;
+      for (const bt_field& cand : f)
+        if (strcmp(cand.key, c.key) == 0) { fi = &cand; break; }
+      if (!fi) return fail(BT_E_SCHEMA, "message lacks field '%s'", c.key);
+    }
+    uint8_t* dst = base + c.slot_off + c.item_bytes * (uint64_t)item;
+    switch (c.kind) {
+      case BT_KIND_NDARRAY: {
+        const bool by_ref = fi->kind == BT_KIND_SHMREF;
+        if ((fi->kind != BT_KIND_NDARRAY && !by_ref) || fi->dtype != c.dtype || fi->ndim != c.ndim || fi->fortran ||
+            memcmp(fi->shape, c.shape, sizeof(int64_t) * c.ndim) != 0 || field_bytes(*fi) != c.item_bytes)
+          return fail(BT_E_SCHEMA, "field '%s' changed type or shape", c.key);
+        if (!by_ref) {
+          memcpy(dst, msg + fi->payload_off, c.item_bytes);
+          break;
+        }
+        bt_shm* seg = nullptr;
+        int rc = shm_attach_cached(reinterpret_cast<const char*>(msg + fi->payload_off), fi->payload_len,
+                                   refs ? device : -1, &seg);
+        if (rc != BT_OK) return rc;
+        const int slot = (int)fi->ival;
+        if (slot >= bt_shm_nslots(seg) || c.item_bytes > bt_shm_slot_bytes(seg))
+          return fail(BT_E_SCHEMA, "field '%s': shared-memory reference out of range", c.key);
+        if (refs) {
+          refs->push_back(PendingRef{seg, slot, (int)ci, item, c.item_bytes});
+        } else {
+          memcpy(dst, bt_shm_slot_ptr(seg, slot), c.item_bytes);
+          bt_shm_release(seg, slot);
+        }
+        break;
+      }
+      case BT_KIND_INT: {
+        if (fi->kind != BT_KIND_INT) return fail(BT_E_SCHEMA, "field '%s' is no longer an int", c.key);
+        memcpy(dst, &fi->ival, 8);
+        break;
+      }
+      case BT_KIND_FLOAT: {
+        double v;
+        if (fi->kind == BT_KIND_FLOAT) v = fi->fval;
+        else if (fi->kind == BT_KIND_INT) v = (double)fi->ival;
+        else return fail(BT_E_SCHEMA, "field '%s' is no longer a float", c.key);
+        memcpy(dst, &v, 8);
+        break;
+      }
+      case BT_KIND_BOOL: {
+        if (fi->kind != BT_KIND_BOOL) return fail(BT_E_SCHEMA, "field '%s' is no longer a bool", c.key);
+        *dst = (uint8_t)(fi->ival != 0);
+        break;
+      }
+    }
+  }
+  return BT_OK;
+}
+
 }  // namespace bt
 
 using namespace bt;
-
-struct bt_schema {
-  std::vector<bt_column> cols;
-  int batch = 0;
-  uint64_t slot_bytes = 0;
-};
 
 extern "C" {
 
@@ -485,13 +577,14 @@ int bt_schema_create(const uint8_t* first_msg, uint64_t len, int batch, bt_schem
     bt_column c;
     memset(&c, 0, sizeof c);
     memcpy(c.key, fi.key, BT_MAX_KEY);
-    c.kind = fi.kind;
+    c.kind = fi.kind == BT_KIND_SHMREF ? BT_KIND_NDARRAY : fi.kind;
     switch (fi.kind) {
       case BT_KIND_NDARRAY:
+      case BT_KIND_SHMREF:
         if (fi.fortran) { delete s; return fail(BT_E_UNSUPPORTED, "field '%s' is Fortran-ordered", fi.key); }
         c.dtype = fi.dtype; c.ndim = fi.ndim;
         memcpy(c.shape, fi.shape, sizeof c.shape);
-        c.item_bytes = fi.payload_len;
+        c.item_bytes = field_bytes(fi);
         break;
       case BT_KIND_INT: c.dtype = BT_I64; c.item_bytes = 8; break;
       case BT_KIND_FLOAT: c.dtype = BT_F64; c.item_bytes = 8; break;
@@ -524,48 +617,7 @@ int bt_schema_ingest(const bt_schema* s, void* slot_base, int item, const uint8_
   std::vector<bt_field>& f = tls_fields();
   int rc = scan_fields(msg, len, f);
   if (rc != BT_OK) return rc;
-  if (f.size() != s->cols.size())
-    return fail(BT_E_SCHEMA, "message has %zu fields, schema has %zu", f.size(), s->cols.size());
-  uint8_t* base = static_cast<uint8_t*>(slot_base);
-  for (size_t ci = 0; ci < s->cols.size(); ++ci) {
-    const bt_column& c = s->cols[ci];
-    const bt_field* fi = &f[ci];
-    if (strcmp(fi->key, c.key) != 0) {  // same keys in another order
-      fi = nullptr;
-      for (const bt_field& cand : f)
-        if (strcmp(cand.key, c.key) == 0) { fi = &cand; break; }
-      if (!fi) return fail(BT_E_SCHEMA, "message lacks field '%s'", c.key);
-    }
-    uint8_t* dst = base + c.slot_off + c.item_bytes * (uint64_t)item;
-    switch (c.kind) {
-      case BT_KIND_NDARRAY: {
-        if (fi->kind != BT_KIND_NDARRAY || fi->dtype != c.dtype || fi->ndim != c.ndim || fi->fortran ||
-            memcmp(fi->shape, c.shape, sizeof(int64_t) * c.ndim) != 0 || fi->payload_len != c.item_bytes)
-          return fail(BT_E_SCHEMA, "field '%s' changed type or shape", c.key);
-        memcpy(dst, msg + fi->payload_off, c.item_bytes);
-        break;
-      }
-      case BT_KIND_INT: {
-        if (fi->kind != BT_KIND_INT) return fail(BT_E_SCHEMA, "field '%s' is no longer an int", c.key);
-        memcpy(dst, &fi->ival, 8);
-        break;
-      }
-      case BT_KIND_FLOAT: {
-        double v;
-        if (fi->kind == BT_KIND_FLOAT) v = fi->fval;
-        else if (fi->kind == BT_KIND_INT) v = (double)fi->ival;
-        else return fail(BT_E_SCHEMA, "field '%s' is no longer a float", c.key);
-        memcpy(dst, &v, 8);
-        break;
-      }
-      case BT_KIND_BOOL: {
-        if (fi->kind != BT_KIND_BOOL) return fail(BT_E_SCHEMA, "field '%s' is no longer a bool", c.key);
-        *dst = (uint8_t)(fi->ival != 0);
-        break;
-      }
-    }
-  }
-  return BT_OK;
+  return place_fields(s, static_cast<uint8_t*>(slot_base), item, msg, f, nullptr, -1);
 }
 
 int bt_schema_ingest_many(const bt_schema* s, void* slot_base, int first_item, int n,

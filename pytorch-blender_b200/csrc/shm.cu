@@ -1,0 +1,235 @@
+// Shared-memory wire for co-located producers.  No reference counterpart:
+// the reference's only transport is the pickled ZMQ message (pkg_blender/blendtorch/btb/publisher.py:43).
+//
+// Segment layout (POSIX shm, name "/btshm_..."):
+//   [Header 64 B][SlotState 64 B x nslots][pad to 4096][slot 0][slot 1]...      slots are 4096-aligned
+// A slot is BUSY from the producer's bt_shm_acquire until the consumer's bt_shm_release.  There is
+// one producer per segment, so acquire needs no CAS: it waits for `busy == 0` (acquire load) on the
+// next slot in round-robin order and then owns it.  The consumer page-locks the whole mapping once
+// with cudaHostRegister, after which slots are valid DMA sources for cudaMemcpyAsync.
+#include <cuda_runtime.h>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <time.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <cerrno>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <new>
+#include <string>
+
+#include "common.h"
+
+namespace {
+
+constexpr uint64_t kMagic = 0x314d485354425f5fULL;  // "__BTSHM1"
+
+struct Header {
+  uint64_t magic;
+  uint32_t version, nslots;
+  uint64_t slot_bytes;
+  uint64_t data_off;
+  uint8_t pad[32];
+};
+static_assert(sizeof(Header) == 64, "header is one cache line");
+
+struct SlotState {
+  std::atomic<uint32_t> busy;
+  uint32_t pad0;
+  std::atomic<uint64_t> since_ns;  // CLOCK_MONOTONIC time of the acquire that made it busy
+  uint8_t pad[48];
+};
+static_assert(sizeof(SlotState) == 64, "one cache line per slot");
+
+}  // namespace
+
+struct bt_shm {
+  std::string name;
+  uint8_t* base = nullptr;
+  uint64_t bytes = 0;
+  Header* hdr = nullptr;
+  SlotState* state = nullptr;
+  bool creator = false;
+  bool registered = false;
+  uint32_t next = 0;
+};
+
+namespace {
+
+std::mutex g_mu;
+std::map<std::string, bt_shm*> g_attached;
+
+int map_segment(const char* name, bool create, uint64_t slot_bytes, int nslots, bt_shm** out) {
+  if (!name || name[0] != '/') return bt::fail(BT_E_INVALID, "shared-memory names start with '/'");
+  int fd = create ? shm_open(name, O_CREAT | O_EXCL | O_RDWR, 0600) : shm_open(name, O_RDWR, 0600);
+  if (fd < 0) return bt::fail(BT_E_IO, "shm_open(%s): %s", name, strerror(errno));
+  uint64_t bytes = 0, data_off = 0;
+  if (create) {
+    slot_bytes = bt::align_up(slot_bytes, 4096);
+    data_off = bt::align_up(sizeof(Header) + sizeof(SlotState) * (uint64_t)nslots, 4096);
+    bytes = data_off + slot_bytes * (uint64_t)nslots;
+    if (ftruncate(fd, (off_t)bytes) != 0) {
+      int e = errno;
+      close(fd);
+      shm_unlink(name);
+      return bt::fail(BT_E_IO, "ftruncate(%s, %llu): %s", name, (unsigned long long)bytes, strerror(e));
+    }
+  } else {
+    struct stat st;
+    if (fstat(fd, &st) != 0 || (uint64_t)st.st_size < sizeof(Header)) {
+      close(fd);
+      return bt::fail(BT_E_IO, "segment %s is not a blendtorch segment", name);
+    }
+    bytes = (uint64_t)st.st_size;
+  }
+  void* p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED | (create ? MAP_POPULATE : 0), fd, 0);
+  close(fd);
+  if (p == MAP_FAILED) {
+    if (create) shm_unlink(name);
+    return bt::fail(BT_E_NOMEM, "mmap(%s, %llu bytes): %s", name, (unsigned long long)bytes, strerror(errno));
+  }
+  bt_shm* s = new (std::nothrow) bt_shm();
+  if (!s) { munmap(p, bytes); return bt::fail(BT_E_NOMEM, "out of memory"); }
+  s->name = name;
+  s->base = static_cast<uint8_t*>(p);
+  s->bytes = bytes;
+  s->hdr = reinterpret_cast<Header*>(s->base);
+  s->state = reinterpret_cast<SlotState*>(s->base + sizeof(Header));
+  s->creator = create;
+  if (create) {
+    memset(s->base, 0, data_off);
+    s->hdr->version = 1;
+    s->hdr->nslots = (uint32_t)nslots;
+    s->hdr->slot_bytes = slot_bytes;
+    s->hdr->data_off = data_off;
+    std::atomic_thread_fence(std::memory_order_release);
+    s->hdr->magic = kMagic;
+  } else {
+    const Header* h = s->hdr;
+    if (h->magic != kMagic || h->version != 1 || h->nslots == 0 ||
+        h->data_off + h->slot_bytes * (uint64_t)h->nslots > bytes) {
+      munmap(p, bytes);
+      delete s;
+      return bt::fail(BT_E_IO, "segment %s has an unknown layout", name);
+    }
+  }
+  *out = s;
+  return BT_OK;
+}
+
+}  // namespace
+
+namespace bt {
+
+int shm_attach_cached(const char* name, size_t name_len, int device, bt_shm** out) {
+  std::string key(name, name_len);
+  std::lock_guard<std::mutex> lock(g_mu);
+  bt_shm* s = nullptr;
+  auto it = g_attached.find(key);
+  if (it != g_attached.end()) {
+    s = it->second;
+  } else {
+    int rc = map_segment(key.c_str(), false, 0, 0, &s);
+    if (rc != BT_OK) return rc;
+    g_attached[key] = s;
+  }
+  if (device >= 0 && !s->registered) {
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaHostRegister(s->base, s->bytes, cudaHostRegisterPortable);
+    if (e != cudaSuccess)
+      return fail(BT_E_CUDA, "cudaHostRegister(%s, %llu bytes) failed: %s", key.c_str(),
+                  (unsigned long long)s->bytes, cudaGetErrorString(e));
+    s->registered = true;
+  }
+  *out = s;
+  return BT_OK;
+}
+
+}  // namespace bt
+
+extern "C" {
+
+int bt_shm_create(const char* name, uint64_t slot_bytes, int nslots, bt_shm** out) {
+  if (!out || slot_bytes == 0 || nslots < 1 || nslots > 65536) return bt::fail(BT_E_INVALID, "bt_shm_create: bad arguments");
+  return map_segment(name, true, slot_bytes, nslots, out);
+}
+
+int bt_shm_attach(const char* name, int device, bt_shm** out) {
+  if (!name || !out) return bt::fail(BT_E_INVALID, "bt_shm_attach: bad arguments");
+  return bt::shm_attach_cached(name, strlen(name), device, out);
+}
+
+int bt_shm_close(bt_shm* s) {
+  if (!s) return BT_OK;
+  {
+    std::lock_guard<std::mutex> lock(g_mu);
+    auto it = g_attached.find(s->name);
+    if (it != g_attached.end() && it->second == s) g_attached.erase(it);
+  }
+  if (s->registered) cudaHostUnregister(s->base);
+  munmap(s->base, s->bytes);
+  if (s->creator) shm_unlink(s->name.c_str());
+  delete s;
+  return BT_OK;
+}
+
+int bt_shm_nslots(const bt_shm* s) { return s ? (int)s->hdr->nslots : bt::fail(BT_E_INVALID, "null segment"); }
+uint64_t bt_shm_slot_bytes(const bt_shm* s) { return s ? s->hdr->slot_bytes : 0; }
+
+void* bt_shm_slot_ptr(bt_shm* s, int slot) {
+  if (!s || slot < 0 || slot >= (int)s->hdr->nslots) {
+    bt::fail(BT_E_INVALID, "bt_shm_slot_ptr: bad slot");
+    return nullptr;
+  }
+  return s->base + s->hdr->data_off + s->hdr->slot_bytes * (uint64_t)slot;
+}
+
+static uint64_t now_ns() {
+  struct timespec t;
+  clock_gettime(CLOCK_MONOTONIC, &t);
+  return (uint64_t)t.tv_sec * 1000000000ull + (uint64_t)t.tv_nsec;
+}
+
+// A slot whose consumer never released it (it exited with the message still queued) is taken back
+// after this long.  Live consumers hold slots for milliseconds.
+static const uint64_t kLeaseNs = 30ull * 1000000000ull;
+
+int bt_shm_acquire(bt_shm* s, int timeout_ms, int* slot) {
+  if (!s || !slot) return bt::fail(BT_E_INVALID, "bt_shm_acquire: bad arguments");
+  const uint32_t n = s->hdr->nslots;
+  const uint64_t t0 = now_ns();
+  unsigned spins = 0;
+  while (true) {
+    // first free slot at or after `next`: a slot that is still held does not block the others
+    const uint64_t now = now_ns();
+    for (uint32_t k = 0; k < n; ++k) {
+      const uint32_t i = (s->next + k) % n;
+      SlotState& st = s->state[i];
+      const bool free_now = st.busy.load(std::memory_order_acquire) == 0;
+      if (free_now || now - st.since_ns.load(std::memory_order_relaxed) > kLeaseNs) {
+        st.since_ns.store(now, std::memory_order_relaxed);
+        st.busy.store(1, std::memory_order_relaxed);
+        s->next = (i + 1) % n;
+        *slot = (int)i;
+        return BT_OK;
+      }
+    }
+    if (++spins < 100) continue;
+    struct timespec nap = {0, 20000};  // 20 us
+    nanosleep(&nap, nullptr);
+    if (timeout_ms >= 0 && (now_ns() - t0) / 1000000ull > (uint64_t)timeout_ms)
+      return bt::fail(BT_E_TIMEOUT, "no free shared-memory slot within %d ms (consumers stalled?)", timeout_ms);
+  }
+}
+
+int bt_shm_release(bt_shm* s, int slot) {
+  if (!s || slot < 0 || slot >= (int)s->hdr->nslots) return bt::fail(BT_E_INVALID, "bt_shm_release: bad slot");
+  s->state[slot].busy.store(0, std::memory_order_release);
+  return BT_OK;
+}
+
+}  // extern "C"

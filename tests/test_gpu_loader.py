@@ -157,3 +157,50 @@ def test_stream_timeout_and_string_fields():
         assert bs[1]["image"].shape == (2, 4, 8, 4) and int(bs[1]["image"][1, 0, 0, 0]) == 3
     finally:
         pr.join(timeout=10)
+
+
+def _shm_publisher(addr, btid, count, slots, h, w):
+    S.run_publisher(addr, btid, 2, h, w, 4, count=count, pool=8, protocol=3, lingerms=10000, shm_slots=slots)
+
+
+@pytest.mark.parametrize("slots,receivers", [(16, 2), (2, 1)])
+def test_stream_shared_memory_wire(slots, receivers, tmp_path):
+    """Opt-in shared-memory wire: payloads reach the GPU by DMA from the producer's segment.  With
+    only 2 slots and batches of 4 the consumer must spill held slots when the stream stalls, or
+    producer and consumer would wait for each other forever."""
+    H, W, pubs = 64, 128, 2
+    per_pub = 16
+    addrs = ["tcp://127.0.0.1:%d" % _free_port() for _ in range(pubs)]
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=_shm_publisher, args=(a, i, -1, slots, H, W), daemon=True) for i, a in enumerate(addrs)]
+    for p in procs:
+        p.start()
+    try:
+        total = per_pub * pubs
+        ds = btt.RemoteIterableDataset(addrs, max_items=total, timeoutms=30000)
+        dl = btt.DeviceLoader(ds, batch_size=4, device=DEV, num_receivers=receivers, keep_raw=True,
+                              preprocess=btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5))
+        expected = {}
+        for btid in range(pubs):
+            rng = S.rng_for(2, btid)
+            for i in range(8):
+                expected[(btid, i)] = S.message(rng, 2, btid, i, H, W)
+        n = 0
+        for b in dl:
+            raw = b["image_raw"].cpu().numpy()
+            np.testing.assert_array_equal(b["image"].cpu().numpy(),
+                                          opre.preprocess_batch(list(raw), flip=True, gamma=2.2, mean=127.5, std=127.5))
+            for i in range(len(raw)):
+                m = expected[(int(b["btid"][i]), int(b["frameid"][i]))]
+                np.testing.assert_array_equal(raw[i], m["image"])
+                np.testing.assert_array_equal(b["bbox"][i].cpu().numpy(), m["bbox"])
+                n += 1
+        assert n == total and dl.stats["compat_items"] == 0
+    finally:
+        for p in procs:
+            p.terminate()
+            p.join(timeout=10)
+        import glob, os
+        for p in procs:
+            for f in glob.glob("/dev/shm/btshm_%d_*" % p.pid):
+                os.unlink(f)
