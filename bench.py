@@ -402,7 +402,7 @@ def ours(args):
     # same leg over the opt-in shared-memory wire (payload by DMA from the producers' segments)
     barrier()
     shm_images, shm_sec, _, _ = e2e_leg(torch, btt, dev, args.steps, args.warmup, sampler, args.transport,
-                                        args.receivers, shm_slots=args.shm_slots)
+                                        args.shm_receivers, shm_slots=args.shm_slots)
     barrier()
     shm_sec = max_over_ranks(shm_sec)
     shm_value = sum_over_ranks(shm_images) / shm_sec
@@ -443,7 +443,8 @@ def ours(args):
                              "frac_of_pcie_h2d": shm_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value,
                              "note": "opt-in wire for co-located producers (DataPublisher(shm_slots=%d)): payload goes "
                                      "producer -> shared memory -> DMA, no consumer-side CPU copy; not the reference's "
-                                     "pickle wire, reported beside e2e, not instead of it" % args.shm_slots},
+                                     "pickle wire, reported beside e2e, not instead of it" % args.shm_slots,
+                             "receivers": args.shm_receivers},
             "gpu_launches": args.steps, "gpu_launches_e2e": args.steps,
             "clocks": clocks,
             "cpu_baseline": cpu,
@@ -465,6 +466,7 @@ def main():
     ap.add_argument("--receivers", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shm-slots", type=int, default=32)
+    ap.add_argument("--shm-receivers", type=int, default=2)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

@@ -31,7 +31,7 @@ from . import native as N
 from . import shm
 from .dataset import FileDataset, RemoteIterableDataset, open_pull_socket
 from .file import FileRecorder
-from .preprocess import Preprocess, preprocess_images
+from .preprocess import PreparedPreprocess, Preprocess
 from .rx import Receiver
 from .staging import Ring, Schema
 
@@ -49,17 +49,32 @@ def _torch_dtype(np_dtype):
 
 
 class _Stager:
-    """One pinned ring + one CUDA stream; turns filled slots into device batches."""
+    """One pinned ring + one CUDA stream; turns filled slots into device batches.
+
+    Everything that is the same for every batch (column views, kernel parameter blocks) is planned
+    once; `finish` is then a handful of torch calls and two ctypes calls.  The owning thread makes
+    `self.stream` its current torch stream, so allocations belong to that stream."""
 
     def __init__(self, schema, device, depth, specs, keep_raw):
         self.schema = schema
         self.device = device
         self.ring = Ring(schema.slot_bytes, depth, device.index)
         self.stream = torch.cuda.Stream(device)
-        self.specs = specs
+        torch.cuda.set_stream(self.stream)      # thread-local: this receiver thread only
+        self._stream_handle = C.c_void_p(self.stream.cuda_stream)
         self.keep_raw = keep_raw
-        self._scratch = None
         self.kernels = 0
+        self.plan = []
+        for c in schema.columns:
+            spec = specs.get(c.key)
+            prep = None
+            if spec is not None:
+                shp = c.shape if len(c.shape) == 3 else c.shape + (1,)
+                if len(shp) != 3:
+                    raise ValueError("field %r has shape %s; frames are (H,W,C) or (H,W)" % (c.key, list(c.shape)))
+                prep = PreparedPreprocess(spec, shp[0], shp[1], shp[2], device)
+            self.plan.append((c.key, c.slot_off, c.item_bytes, _torch_dtype(c.dtype), c.shape, prep))
+        self.item_bytes = sum(c.item_bytes for c in schema.columns)
 
     def begin(self):
         return self.ring.acquire()
@@ -70,32 +85,33 @@ class _Stager:
     def finish(self, slot, n, host_rows):
         sch = self.schema
         used = 0
-        for c in sch.columns:
-            used = max(used, c.slot_off + n * c.item_bytes)
+        for _, off, ib, _, _, _ in self.plan:
+            used = max(used, off + n * ib)
         batch = {}
-        with torch.cuda.stream(self.stream):
-            raw = torch.empty(max(used, 1), dtype=torch.uint8, device=self.device)
-            if used:
-                self.ring.submit_batch(slot, sch, n, raw.data_ptr(), C.c_void_p(self.stream.cuda_stream))
-            for c in sch.columns:
-                t = raw[c.slot_off:c.slot_off + n * c.item_bytes].view(_torch_dtype(c.dtype)).view((n,) + c.shape)
-                spec = self.specs.get(c.key)
-                if spec is not None:
-                    if self._scratch is None and spec.stats:
-                        self._scratch = torch.empty(1 << 17, dtype=torch.uint8, device=self.device)
-                    res = preprocess_images(t, spec, stream=self.stream, _scratch=self._scratch)
-                    self.kernels += 1
-                    if spec.stats:
-                        res, batch[c.key + "_stats"] = res
-                    if self.keep_raw:
-                        batch[c.key + "_raw"] = t
-                    t = res
-                batch[c.key] = t
-            ev = torch.cuda.Event()
-            ev.record(self.stream)
+        raw = torch.empty(max(used, 1), dtype=torch.uint8, device=self.device)
+        if used:
+            self.ring.submit_batch(slot, sch, n, raw.data_ptr(), self._stream_handle)
+        keep = [raw]                       # distinct storages the consumer stream must know about
+        base = raw.data_ptr()
+        for key, off, ib, dt, shape, prep in self.plan:
+            if prep is None or self.keep_raw:
+                t = raw[off:off + n * ib].view(dt).view((n,) + shape)
+            if prep is not None:
+                out, stats = prep.run(base + off, n, self._stream_handle)
+                self.kernels += 1
+                keep.append(out)
+                if stats is not None:
+                    batch[key + "_stats"] = stats
+                    keep.append(stats)
+                if self.keep_raw:
+                    batch[key + "_raw"] = t
+                t = out
+            batch[key] = t
+        ev = torch.cuda.Event()
+        ev.record(self.stream)
         for k in sch.host_keys:
             batch[k] = host_rows.get(k, [])
-        return batch, ev
+        return batch, ev, keep
 
     def close(self):
         self.stream.synchronize()
@@ -177,11 +193,11 @@ class DeviceLoader:
         return _Stager(schema, self.device, self.ring_depth, self.specs, self.keep_raw)
 
     def _emit(self, out_q, stop, stager, slot, n, host_rows):
-        batch, ev = stager.finish(slot, n, host_rows)
-        self.stats["bytes_h2d"] += sum(c.item_bytes for c in stager.schema.columns) * n
+        item = stager.finish(slot, n, host_rows)
+        self.stats["bytes_h2d"] += stager.item_bytes * n
         while not stop.is_set():
             try:
-                out_q.put((batch, ev), timeout=0.1)
+                out_q.put(item, timeout=0.1)
                 return True
             except queue.Full:
                 continue
@@ -423,14 +439,13 @@ class DeviceLoader:
                     continue
                 if isinstance(item, BaseException):
                     raise item
-                batch, ev = item
+                batch, ev, keep = item
                 cur = torch.cuda.current_stream(self.device)
                 cur.wait_event(ev)
-                for v in batch.values():
-                    if isinstance(v, torch.Tensor):
-                        v.record_stream(cur)
+                for t in keep:
+                    t.record_stream(cur)
                 self.stats["batches"] += 1
-                self.stats["items"] += next((len(v) for v in batch.values()), 0)
+                self.stats["items"] += len(batch["btid"]) if "btid" in batch else next((len(v) for v in batch.values()), 0)
                 yield batch
         finally:
             stop.set()

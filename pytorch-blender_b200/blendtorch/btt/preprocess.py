@@ -144,3 +144,57 @@ def preprocess_images(src, spec, out=None, stream=None, stats_out=None, _scratch
     with torch.cuda.device(src.device):
         N.check(N.lib.bt_preprocess_launch(C.byref(p), _stream_handle(stream)))
     return (out, stats) if spec.stats else out
+
+
+class PreparedPreprocess:
+    """`preprocess_images` for a fixed frame shape with everything that does not change from batch
+    to batch (parameter struct, gamma table, statistics scratch) set up once -- the per-batch cost
+    of the host side is two allocations and one ctypes call.  Used by DeviceLoader."""
+
+    def __init__(self, spec, height, width, channels, device):
+        if not 1 <= channels <= 4:
+            raise ValueError("channels must be 1..4")
+        self.spec, self.device = spec, device
+        self.h, self.w, self.c = height, width, channels
+        self.cout = spec.out_channels or channels
+        if not 1 <= self.cout <= channels:
+            raise ValueError("out_channels must be within 1..channels")
+        p = N.PreprocessParams()
+        p.height, p.width, p.channels, p.out_channels = height, width, channels, self.cout
+        p.out_dtype = _TORCH_OUT[spec.dtype]
+        p.flip, p.chw = int(bool(spec.flip)), int(spec.layout == "NCHW")
+        p.use_gamma = int(bool(spec.gamma))
+        p.use_norm = int(spec.mean is not None or spec.std is not None)
+        p.variant, p.reserved = VARIANTS[spec.variant], int(spec.tune)
+        p.src_image_stride = 0
+        mean, std = _per_channel(spec.mean, 0.0), _per_channel(spec.std, 1.0)
+        for c in range(4):
+            p.mean[c], p.stdev[c] = mean[c], std[c]
+        if spec.gamma:
+            C.memmove(p.gamma_lut, spec._lut, 256)
+        self.params = p
+        self._ref = C.byref(p)
+        self.scratch = None
+        if spec.stats:
+            p.stats_out = 1  # non-null so that the size query answers for the statistics path
+            self.scratch = torch.empty(N.lib.bt_preprocess_scratch_bytes(self._ref), dtype=torch.uint8, device=device)
+            p.stats_scratch = self.scratch.data_ptr()
+            p.stats_out = None
+
+    def out_shape(self, n):
+        return (n, self.cout, self.h, self.w) if self.spec.layout == "NCHW" else (n, self.h, self.w, self.cout)
+
+    def run(self, src_ptr, n, stream_handle):
+        """Launch on `n` dense frames at device address `src_ptr`; allocations come from torch's
+        *current* stream, which the caller has set to the stream behind `stream_handle`."""
+        out = torch.empty(self.out_shape(n), dtype=self.spec.dtype, device=self.device)
+        stats = None
+        p = self.params
+        if self.spec.stats:
+            stats = torch.empty((self.cout, 2), dtype=torch.float64, device=self.device)
+            p.stats_out = stats.data_ptr()
+        if n == 0:
+            return out, (stats.zero_() if stats is not None else None)
+        p.src, p.dst, p.batch = src_ptr, out.data_ptr(), n
+        N.check(N.lib.bt_preprocess_launch(self._ref, stream_handle))
+        return out, stats

@@ -24,9 +24,13 @@ def main():
               ("ipc", 2, 5), ("ipc", 3, 5), ("ipc", 6, 2)]
     if len(sys.argv) > 1:
         combos = [tuple(int(x) if x.isdigit() else x for x in a.split(",")) for a in sys.argv[1:]]
-    for transport, recv, io in combos:
-        images, sec, h2d, d2h = bench.e2e_leg(torch, btt, dev, 600, 10, _S(), transport, recv, io)
-        r = {"transport": transport, "receivers": recv, "io_threads": io, "images_per_s": images / sec,
+    for combo in combos:
+        transport, recv, io = combo[:3]
+        shm_slots = combo[3] if len(combo) > 3 else 0
+        bench.PUBLISHERS = combo[4] if len(combo) > 4 else 5
+        images, sec, h2d, d2h = bench.e2e_leg(torch, btt, dev, 600, 10, _S(), transport, recv, io, shm_slots)
+        r = {"transport": transport, "receivers": recv, "io_threads": io, "shm_slots": shm_slots,
+             "publishers": bench.PUBLISHERS, "images_per_s": images / sec,
              "GBps": images / sec * 1228800 / 1e9}
         print(json.dumps(r), flush=True)
         res.append(r)
