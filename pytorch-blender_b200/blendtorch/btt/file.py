@@ -105,7 +105,10 @@ class FileReader:
     def _ensure_map(self):
         if self._map is None:
             with io.open(self.path, "rb") as f:
-                self._map = mmap.mmap(f.fileno(), 0, access=mmap.ACCESS_READ)
+                # pre-fault the mapping: replay touches every page, and a page fault per 4 KiB
+                # in the copy loop would cap it at a few GB/s
+                flags = mmap.MAP_SHARED | getattr(mmap, "MAP_POPULATE", 0)
+                self._map = mmap.mmap(f.fileno(), 0, flags=flags, prot=mmap.PROT_READ)
             size = len(self._map)
             ends = np.empty(len(self.offsets), dtype=np.int64)
             if len(ends):

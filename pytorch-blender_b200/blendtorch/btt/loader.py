@@ -163,6 +163,7 @@ class DeviceLoader:
         self.seed, self.keep_raw = seed, keep_raw
         self.io_threads = max(1, int(io_threads))
         self._epoch = 0
+        self._stagers = {}
         self.stats = {"batches": 0, "items": 0, "bytes_h2d": 0, "kernels": 0, "compat_items": 0}
         if isinstance(dataset, RemoteIterableDataset):
             if shuffle:
@@ -184,13 +185,54 @@ class DeviceLoader:
         return n // self.batch_size if self.drop_last else -(-n // self.batch_size)
 
     # ---- producers --------------------------------------------------------------------------
-    def _new_stager(self, first_msg):
+    def _new_stager(self, first_msg, rid=0):
+        """Stager for the stream that starts with `first_msg`.  Pinned rings are expensive to create
+        (page-locking hundreds of MB takes longer than an epoch of small recordings), so a stager
+        is kept per producer and reused by later epochs while the layout stays the same."""
         schema = Schema.from_message(first_msg, self.batch_size)
         for key in self.specs:
             c = schema.column(key)  # KeyError: the named image field is not in the messages
             if c.dtype != np.uint8:
                 raise TypeError("field %r is %s; preprocessing takes uint8 frames" % (key, c.dtype))
-        return _Stager(schema, self.device, self.ring_depth, self.specs, self.keep_raw)
+        sig = (schema.native, tuple((c.key, c.kind, c.dtype.str, c.shape, c.slot_off) for c in schema.columns),
+               schema.host_keys)
+        cached = self._stagers.get(rid)
+        if cached is not None and cached[0] == sig:
+            schema.close()
+            stager = cached[1]
+            torch.cuda.set_stream(stager.stream)   # a new thread runs this epoch
+            return stager
+        if cached is not None:
+            cached[1].close()
+        stager = _Stager(schema, self.device, self.ring_depth, self.specs, self.keep_raw)
+        self._stagers[rid] = (sig, stager)
+        return stager
+
+    @staticmethod
+    def _rid():
+        name = threading.current_thread().name          # "bt-recv-<k>"
+        return int(name.rsplit("-", 1)[-1]) if name.startswith("bt-recv-") else 0
+
+    def _retire(self, stager):
+        """End of an epoch: keep cached stagers (their ring), close the others."""
+        if stager is None:
+            return
+        self.stats["kernels"] += stager.kernels
+        stager.kernels = 0
+        if not any(v[1] is stager for v in self._stagers.values()):
+            stager.close()
+
+    def close(self):
+        """Release pinned rings and streams kept between epochs."""
+        for _, st in self._stagers.values():
+            st.close()
+        self._stagers = {}
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def _emit(self, out_q, stop, stager, slot, n, host_rows):
         item = stager.finish(slot, n, host_rows)
@@ -237,9 +279,7 @@ class DeviceLoader:
                     pass
                 sock.close()
             ctx.term()
-            if stager is not None:
-                self.stats["kernels"] += stager.kernels
-                stager.close()
+            self._retire(stager)
             out_q.put(_DONE)
 
     def _stream_fast(self, ds, sock, out_q, stop, holder):
@@ -256,7 +296,7 @@ class DeviceLoader:
                 assert waited < ds.timeoutms, "No response within timeout interval."
             if remaining <= 0:
                 return
-            stager = self._new_stager(rx.pending())
+            stager = self._new_stager(rx.pending(), self._rid())
             holder.append(stager)
             ring, schema = stager.ring, stager.schema
             while remaining > 0 and not stop.is_set():
@@ -343,7 +383,7 @@ class DeviceLoader:
                 self.stats["compat_items"] += 1
             else:
                 if stager is None:
-                    stager = self._new_stager(msg)
+                    stager = self._new_stager(msg, self._rid())
                     holder.append(stager)
                 if slot is None:
                     slot, filled, host_rows = stager.begin(), 0, {}
@@ -398,7 +438,7 @@ class DeviceLoader:
                         m = fidx == f
                         addrs[m], lens[m] = readers[f].spans(local[m])
                     if stager is None:
-                        stager = self._new_stager(readers[fidx[0]].raw(int(local[0])))
+                        stager = self._new_stager(readers[fidx[0]].raw(int(local[0])), rid)
                     slot, host_rows = stager.begin(), {}
                     done = 0
                     if stager.schema.native:
@@ -412,9 +452,7 @@ class DeviceLoader:
         except BaseException as e:
             out_q.put(e)
         finally:
-            if stager is not None:
-                self.stats["kernels"] += stager.kernels
-                stager.close()
+            self._retire(stager)
             out_q.put(_DONE)
 
     # ---- consumer ---------------------------------------------------------------------------

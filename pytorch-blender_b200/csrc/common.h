@@ -43,6 +43,11 @@ inline int dtype_size(int dt) {
   } while (0)
 
 // ---- internals shared between scan.cpp, ring.cu and shm.cu --------------------------------------
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
 #include <vector>
 
 struct bt_schema {
@@ -69,8 +74,33 @@ std::vector<bt_field>& tls_fields();
 // Copy the scanned fields of one message into item `item` of the slot at `base`.  Fields that
 // arrive as shared-memory references are appended to `refs` when it is non-null (the caller will
 // DMA them straight from the segment), otherwise they are copied and released here.
+struct CopyTask {
+  uint8_t* dst;
+  const uint8_t* src;
+  uint64_t n;
+};
+
 int place_fields(const bt_schema* s, uint8_t* base, int item, const uint8_t* msg,
-                 const std::vector<bt_field>& f, std::vector<PendingRef>* refs, int device);
+                 const std::vector<bt_field>& f, std::vector<PendingRef>* refs, int device,
+                 std::vector<CopyTask>* tasks = nullptr);
+
+class WorkPool {
+ public:
+  static WorkPool& get();
+  // fn(k) for k in [0, ntasks) on up to `nthreads` threads (the caller is one of them).
+  void run(int nthreads, size_t ntasks, const std::function<void(size_t)>& fn);
+
+ private:
+  void worker(int index);
+  std::mutex mu_, job_mu_;
+  std::condition_variable cv_, done_;
+  std::vector<std::thread> workers_;
+  const std::function<void(size_t)>* fn_ = nullptr;
+  size_t ntasks_ = 0;
+  std::atomic<size_t> next_{0};
+  int limit_ = 0, active_ = 0;
+  uint64_t generation_ = 0;
+};
 
 // Process-wide registry of attached segments (shm.cu).
 int shm_attach_cached(const char* name, size_t name_len, int device, bt_shm** out);

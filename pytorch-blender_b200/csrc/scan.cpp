@@ -484,8 +484,72 @@ uint64_t field_bytes(const bt_field& f) {
   return count * (uint64_t)dtype_size(f.dtype);
 }
 
+namespace {
+constexpr uint64_t kChunk = 256 * 1024;
+void copy_or_defer(uint8_t* dst, const uint8_t* src, uint64_t n, std::vector<CopyTask>* tasks) {
+  if (!tasks || n < 64 * 1024) {
+    memcpy(dst, src, n);
+    return;
+  }
+  for (uint64_t off = 0; off < n; off += kChunk)
+    tasks->push_back(CopyTask{dst + off, src + off, n - off < kChunk ? n - off : kChunk});
+}
+}  // namespace
+
+// Persistent worker threads for bulk copies (replay).  One job at a time; the caller works too.
+WorkPool& WorkPool::get() {
+  static WorkPool* pool = new WorkPool();  // intentionally leaked: workers may outlive static destruction
+  return *pool;
+}
+
+void WorkPool::worker(int index) {
+  uint64_t seen = 0;
+  while (true) {
+    std::unique_lock<std::mutex> lk(mu_);
+    cv_.wait(lk, [&] { return generation_ != seen; });
+    seen = generation_;
+    const bool take_part = index < limit_;
+    lk.unlock();
+    if (take_part) {
+      size_t k;
+      while ((k = next_.fetch_add(1)) < ntasks_) (*fn_)(k);
+      lk.lock();
+      if (--active_ == 0) done_.notify_all();
+    }
+  }
+}
+
+void WorkPool::run(int nthreads, size_t ntasks, const std::function<void(size_t)>& fn) {
+  if (nthreads > 64) nthreads = 64;
+  if (nthreads <= 1 || ntasks <= 1) {
+    for (size_t k = 0; k < ntasks; ++k) fn(k);
+    return;
+  }
+  std::lock_guard<std::mutex> one_job(job_mu_);
+  {
+    std::unique_lock<std::mutex> lk(mu_);
+    while ((int)workers_.size() < nthreads - 1) {
+      const int idx = (int)workers_.size();
+      workers_.emplace_back([this, idx] { worker(idx); });
+      workers_.back().detach();
+    }
+    fn_ = &fn;
+    ntasks_ = ntasks;
+    next_.store(0);
+    limit_ = nthreads - 1;
+    active_ = limit_;
+    ++generation_;
+  }
+  cv_.notify_all();
+  size_t k;
+  while ((k = next_.fetch_add(1)) < ntasks) fn(k);
+  std::unique_lock<std::mutex> lk(mu_);
+  done_.wait(lk, [&] { return active_ == 0; });
+}
+
 int place_fields(const bt_schema* s, uint8_t* base, int item, const uint8_t* msg,
-                 const std::vector<bt_field>& f, std::vector<PendingRef>* refs, int device) {
+                 const std::vector<bt_field>& f, std::vector<PendingRef>* refs, int device,
+                 std::vector<CopyTask>* tasks) {
   if (f.size() != s->cols.size())
     return fail(BT_E_SCHEMA, "message has %zu fields, schema has %zu", f.size(), s->cols.size());
   for (size_t ci = 0; ci < s->cols.size(); ++ci) {
@@ -505,7 +569,7 @@ int place_fields(const bt_schema* s, uint8_t* base, int item, const uint8_t* msg
             memcmp(fi->shape, c.shape, sizeof(int64_t) * c.ndim) != 0 || field_bytes(*fi) != c.item_bytes)
           return fail(BT_E_SCHEMA, "field '%s' changed type or shape", c.key);
         if (!by_ref) {
-          memcpy(dst, msg + fi->payload_off, c.item_bytes);
+          copy_or_defer(dst, msg + fi->payload_off, c.item_bytes, tasks);
           break;
         }
         bt_shm* seg = nullptr;
@@ -626,32 +690,26 @@ int bt_schema_ingest_many(const bt_schema* s, void* slot_base, int first_item, i
   if (!s || !slot_base || !msgs || !lens || n < 0 || first_item < 0 || first_item + n > s->batch)
     return fail(BT_E_INVALID, "bt_schema_ingest_many: bad arguments");
   if (failed_index) *failed_index = -1;
-  if (nthreads > n) nthreads = n;
-  if (nthreads <= 1) {
-    for (int i = 0; i < n; ++i) {
-      int rc = bt_schema_ingest(s, slot_base, first_item + i, msgs[i], lens[i]);
-      if (rc != BT_OK) { if (failed_index) *failed_index = i; return rc; }
+  // Pass 1 (serial, ~1 us per message): scan every message, write the scalars, and turn every
+  // payload into copy tasks of at most kChunk bytes.  Pass 2: the tasks run on the persistent
+  // pool, so a batch of a few large frames is spread over all threads as evenly as many small ones.
+  static thread_local std::vector<CopyTask> tasks;
+  tasks.clear();
+  std::vector<bt_field>& f = tls_fields();
+  uint8_t* base = static_cast<uint8_t*>(slot_base);
+  for (int i = 0; i < n; ++i) {
+    int rc = scan_fields(msgs[i], lens[i], f);
+    if (rc == BT_OK) rc = place_fields(s, base, first_item + i, msgs[i], f, nullptr, -1, nthreads > 1 ? &tasks : nullptr);
+    if (rc != BT_OK) {
+      if (failed_index) *failed_index = i;
+      return rc;
     }
-    return BT_OK;
   }
-  std::vector<int> rcs(nthreads, BT_OK), bad(nthreads, -1);
-  std::vector<std::string> errs(nthreads);
-  std::vector<std::thread> pool;
-  pool.reserve(nthreads);
-  for (int t = 0; t < nthreads; ++t) {
-    pool.emplace_back([&, t]() {
-      for (int i = t; i < n; i += nthreads) {
-        int rc = bt_schema_ingest(s, slot_base, first_item + i, msgs[i], lens[i]);
-        if (rc != BT_OK) { rcs[t] = rc; bad[t] = i; errs[t] = last_error_ref(); return; }
-      }
-    });
+  if (!tasks.empty()) {
+    const std::vector<CopyTask>& t = tasks;
+    WorkPool::get().run(nthreads, t.size(), [&t](size_t k) { memcpy(t[k].dst, t[k].src, t[k].n); });
   }
-  for (auto& th : pool) th.join();
-  int first_bad = -1, rc = BT_OK;
-  for (int t = 0; t < nthreads; ++t)
-    if (rcs[t] != BT_OK && (first_bad < 0 || bad[t] < first_bad)) { first_bad = bad[t]; rc = rcs[t]; last_error_ref() = errs[t]; }
-  if (failed_index) *failed_index = first_bad;
-  return rc;
+  return BT_OK;
 }
 
 }  // extern "C"
