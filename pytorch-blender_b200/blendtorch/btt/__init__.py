@@ -11,12 +11,12 @@ from .dataset import FileDataset, RemoteIterableDataset, SingleFileDataset
 from .file import FileReader, FileRecorder
 from . import native
 from .preprocess import Preprocess, preprocess_images
-from .camera import Camera
+from .camera import Camera, Projection
 from .loader import DeviceLoader, shard
 from .publisher import DataPublisher
 
 __version__ = "0.2.0+b200.1"
 
 __all__ = ["RemoteIterableDataset", "FileDataset", "SingleFileDataset", "FileRecorder", "FileReader",
-           "DeviceLoader", "Preprocess", "preprocess_images", "Camera", "DataPublisher", "shard",
+           "DeviceLoader", "Preprocess", "preprocess_images", "Camera", "Projection", "DataPublisher", "shard",
            "DEFAULT_TIMEOUTMS", "native"]

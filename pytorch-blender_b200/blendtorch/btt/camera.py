@@ -124,3 +124,48 @@ class Camera:
         if squeeze:
             return o["xy"][0], o["bbox"][0]
         return o["xy"], o["bbox"]
+
+
+class Projection:
+    """Per-batch annotation projection inside `DeviceLoader`: world points carried by the messages
+    (e.g. the 8 corners of every object's bounding box, as `btb.utils.bbox_world_coordinates`
+    yields them, utils.py:84-109) become pixel coordinates, optional depths and optional per-object
+    pixel boxes, by one K2 launch per batch on the loader's stream.
+
+    key:        message field holding the points, shape (N, 3) per frame.
+    camera:     a `Camera` with fixed matrices, or None to take them from the message fields
+                `view_key` / `proj_key` ((4, 4) per frame) with image `shape`.
+    xy_key, depth_key, bbox_key: names of the outputs added to the batch (None = not computed).
+    corners_per_object: group size for `bbox_key` (8 for box corners).
+    """
+
+    def __init__(self, key, camera=None, xy_key="xy", depth_key=None, bbox_key=None, corners_per_object=8,
+                 origin="upper-left", view_key=None, proj_key=None, shape=None):
+        if camera is None and not (view_key and proj_key and shape):
+            raise ValueError("give a Camera, or view_key + proj_key + shape")
+        assert origin in ["upper-left", "lower-left"]
+        self.key, self.camera = key, camera
+        self.xy_key, self.depth_key, self.bbox_key = xy_key, depth_key, bbox_key
+        self.corners_per_object, self.origin = corners_per_object, origin
+        self.view_key, self.proj_key, self.shape = view_key, proj_key, shape
+
+    def apply(self, batch, device):
+        pts = batch[self.key]
+        if pts.dtype != torch.float64:
+            pts = pts.to(torch.float64)
+        pts = pts.contiguous()
+        cam = self.camera
+        if cam is None:
+            cam = Camera.__new__(Camera)
+            cam.device = device
+            cam.view_matrix = batch[self.view_key].to(torch.float64).contiguous()
+            cam.proj_matrix = batch[self.proj_key].to(torch.float64).contiguous()
+            cam.shape = tuple(self.shape)
+        out = cam._launch(pts, False, True, self.depth_key is not None, self.origin,
+                          bbox_corners=self.corners_per_object if self.bbox_key else 0)
+        made = []
+        for name, k in ((self.xy_key, "xy"), (self.depth_key, "z"), (self.bbox_key, "bbox")):
+            if name and k in out:
+                batch[name] = out[k]
+                made.append(out[k])
+        return made

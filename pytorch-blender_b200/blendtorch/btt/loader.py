@@ -55,9 +55,10 @@ class _Stager:
     once; `finish` is then a handful of torch calls and two ctypes calls.  The owning thread makes
     `self.stream` its current torch stream, so allocations belong to that stream."""
 
-    def __init__(self, schema, device, depth, specs, keep_raw):
+    def __init__(self, schema, device, depth, specs, keep_raw, projections=()):
         self.schema = schema
         self.device = device
+        self.projections = projections
         self.ring = Ring(schema.slot_bytes, depth, device.index)
         self.stream = torch.cuda.Stream(device)
         torch.cuda.set_stream(self.stream)      # thread-local: this receiver thread only
@@ -107,6 +108,9 @@ class _Stager:
                     batch[key + "_raw"] = t
                 t = out
             batch[key] = t
+        for pj in self.projections:
+            keep.extend(pj.apply(batch, self.device))
+            self.kernels += 1
         ev = torch.cuda.Event()
         ev.record(self.stream)
         for k in sch.host_keys:
@@ -127,6 +131,8 @@ class DeviceLoader:
     device: CUDA device of this process (one process per GPU; shard publishers/files with `shard`).
     preprocess: a `Preprocess` or list of them (one per image field) run on the GPU; None leaves
         the uint8 frames as they are -- exactly default_collate's output, on the device.
+    project: a `Projection` or list of them: world points carried by the messages are projected to
+        pixels (and per-object boxes) on the GPU, one K2 launch per batch.
     num_receivers: receiver threads for streams; each owns a PULL socket connected to all
         addresses and takes ``max_items // num_receivers`` items, like the reference's DataLoader
         workers (dataset.py:80-85,97).
@@ -140,7 +146,7 @@ class DeviceLoader:
 
     def __init__(self, dataset, batch_size=1, shuffle=False, drop_last=False, device="cuda",
                  preprocess=None, num_receivers=1, ring_depth=3, prefetch=2, ingest_threads=4,
-                 seed=0, keep_raw=False, io_threads=1):
+                 seed=0, keep_raw=False, io_threads=1, project=None):
         self.dataset = dataset
         self.batch_size = int(batch_size)
         if self.batch_size < 1:
@@ -157,6 +163,11 @@ class DeviceLoader:
         elif isinstance(preprocess, Preprocess):
             preprocess = [preprocess]
         self.specs = {p.key: p for p in preprocess}
+        if project is None:
+            project = []
+        elif not isinstance(project, (list, tuple)):
+            project = [project]
+        self.projections = tuple(project)
         self.num_receivers = max(1, int(num_receivers))
         self.ring_depth, self.prefetch = int(ring_depth), int(prefetch)
         self.ingest_threads = int(ingest_threads)
@@ -204,7 +215,7 @@ class DeviceLoader:
             return stager
         if cached is not None:
             cached[1].close()
-        stager = _Stager(schema, self.device, self.ring_depth, self.specs, self.keep_raw)
+        stager = _Stager(schema, self.device, self.ring_depth, self.specs, self.keep_raw, self.projections)
         self._stagers[rid] = (sig, stager)
         return stager
 
@@ -376,7 +387,7 @@ class DeviceLoader:
                 obj = ds._item(obj)
                 if stager is None:
                     stager = _Stager(Schema.from_object(obj, self.batch_size), self.device,
-                                     self.ring_depth, self.specs, self.keep_raw)
+                                     self.ring_depth, self.specs, self.keep_raw, self.projections)
                 if slot is None:
                     slot, filled, host_rows = stager.begin(), 0, {}
                 stager.schema.ingest_object(stager.ring.view(slot), filled, obj, host_rows)
@@ -426,7 +437,7 @@ class DeviceLoader:
                     objs = [ds._item(readers[f][int(l)]) for f, l in zip(fidx, local)]
                     if stager is None:
                         stager = _Stager(Schema.from_object(objs[0], B), self.device, self.ring_depth,
-                                         self.specs, self.keep_raw)
+                                         self.specs, self.keep_raw, self.projections)
                     slot, host_rows = stager.begin(), {}
                     for i, o in enumerate(objs):
                         stager.schema.ingest_object(stager.ring.view(slot), i, o, host_rows)
