@@ -139,6 +139,16 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(self.samples)}
 
 
+def measured_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the headline kernel, from the committed
+    ncu --set full capture (profiles/); None if no capture is there."""
+    f = ROOT / "profiles" / "r1_k1_traffic.json"
+    try:
+        return float(json.loads(f.read_text())["dram_bytes_read_plus_write_per_launch"])
+    except Exception:
+        return None
+
+
 def measured_peaks():
     f = ROOT / "MEASURED_PEAKS.json"
     if f.exists():
@@ -431,7 +441,10 @@ def ours(args):
                        "e2e_transport": args.transport, "e2e_receivers": args.receivers,
                        "parallelism": "dp%d, publishers sharded per GPU, no collective" % world},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": measured_traffic(), "peak_source": peak_src,
+                         "traffic_note": "ncu, cold L2: 9.85 MB read (= algorithmic 9.83 MB) + <0.2 MB written back inside the "
+                                         "kernel; the 39.3 MB of fp32 output of a batch-8 launch are absorbed by the 126 MB L2 "
+                                         "and written back after it (C4-size launches write through: see profiles/)",
                          "kernel": "k1_planar<float,4,4,4>", "algorithmic_bytes_per_launch": algo_bytes,
                          "frac_of_nominal_8TBs": achieved / 8000.0,
                          "large_batch": {"workload": "C4 per-GPU batch: 64 x 1024x1024 RGBA -> fp32 NCHW",
