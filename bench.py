@@ -360,7 +360,19 @@ def ours(args):
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL announces its version on stdout at the first collective; stdout is reserved for the one
+        # JSON line, so send everything to stderr until the communicator is up.
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     import importlib.util
     spec_ = importlib.util.spec_from_file_location("bt_build_native", PKG / "build_native.py")
     mod = importlib.util.module_from_spec(spec_)
@@ -476,12 +488,19 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--transport", default="tcp", choices=["tcp", "ipc"])
-    ap.add_argument("--receivers", type=int, default=4)
+    ap.add_argument("--receivers", type=int, default=0, help="receiver threads per GPU (0 = by host cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shm-slots", type=int, default=32)
     ap.add_argument("--shm-receivers", type=int, default=2)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    if args.receivers <= 0:
+        # receiver threads per GPU: 4 where the host has cores to spare, fewer when N GPUs share few
+        # cores with their N x 5 publisher processes
+        n = max(1, int(os.environ.get("WORLD_SIZE", args.gpus)))
+        spare = (os.cpu_count() or 1) - PUBLISHERS * n
+        args.receivers = min(4, max(1, spare // (2 * n)))
+    args.shm_receivers = min(args.shm_receivers, args.receivers)
     if args.impl == "reference":
         return reference_arm(args)
     return ours(args)
