@@ -244,7 +244,12 @@ __global__ void __launch_bounds__(kThreads) k1_planar(K1Args a, PlanarGeom g) {
   static_assert(UB % 4 == 0, "unit must be whole 32-bit words");
   constexpr int WORDS = UB / 4;
   __shared__ T lut[kMaxC * 256];
+  // Programmatic dependent launch: let the next launch in the stream begin its own prologue now,
+  // build our table while the previous kernel (or copy) drains, and only then wait for it.  Both
+  // instructions are no-ops when the launch carries no programmatic dependency.
+  asm volatile("griddepcontrol.launch_dependents;");
   build_lut<T>(a, lut);
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   StatAcc acc;
   if (STATS) acc.clear();
 
@@ -458,6 +463,26 @@ bool planar_geom(const K1Args& a, int ppt, PlanarGeom& g) {
   return true;
 }
 
+// Launch with or without the programmatic-stream-serialization attribute (PDL).
+template <typename K>
+void launch_planar(K kernel, int grid, cudaStream_t st, const K1Args& a, const PlanarGeom& geo, int pdl) {
+  if (!pdl) {
+    kernel<<<grid, kThreads, 0, st>>>(a, geo);
+    return;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, kernel, a, geo);
+}
+
 template <typename T, bool STATS>
 int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStream_t st, int grid_cap) {
   const int sms = sm_count();
@@ -476,7 +501,7 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
     PlanarGeom geo;                                                                         \
     if (!planar_geom(a, (PPT_), geo)) break; /* too many units for 32-bit indices */        \
     int g = grid_of(geo.total_units, (UNR_));                                               \
-    k1_planar<T, C_, PPT_, UNR_, STATS><<<g, kThreads, 0, st>>>(a, geo);                    \
+    launch_planar(k1_planar<T, C_, PPT_, UNR_, STATS>, g, st, a, geo, !((p->reserved >> 16) & 1)); \
     g_last_variant = 2;                                                                     \
     return g;                                                                               \
   } while (0)

@@ -89,7 +89,14 @@ def main():
         dict(shape=C3, dtype=torch.float32), dict(shape=C5, dtype=torch.float32),
         dict(shape=(8, 480, 640, 3), dtype=torch.float32), dict(shape=(8, 481, 641, 4), dtype=torch.float32),
     ]
-    if len(sys.argv) > 1 and sys.argv[1] == "tune2":
+    if len(sys.argv) > 1 and sys.argv[1] == "pdl":
+        cases = []
+        for shape in (C2, (16, 480, 640, 4), C4):
+            for dt in (torch.float32, torch.bfloat16):
+                for tune in (0, 0x10000):
+                    for streams in (1, 4):
+                        cases.append(dict(shape=shape, dtype=dt, tune=tune, streams=streams))
+    elif len(sys.argv) > 1 and sys.argv[1] == "tune2":
         cases = []
         for shape in (C4, C3, C5, (16, 480, 640, 4), (32, 480, 640, 4)):
             for unroll in (0, 8):
