@@ -19,7 +19,6 @@ Unpickler per open file exactly like file.py:110-112.
 import io
 import logging
 import mmap
-import os
 import pickle
 from pathlib import Path
 
@@ -31,14 +30,21 @@ _HEADER_PROTOCOL = 3  # file.py:63,72 -- readable by Blender's Python 3.7
 
 
 class FileRecorder:
-    """Context manager that appends raw messages to one ``.btr`` file (file.py:10-79)."""
+    """Context manager that appends raw messages to one ``.btr`` file (file.py:10-79).
 
-    def __init__(self, outpath="blendtorch.mpkl", max_messages=100000):
+    `async_write=True` (additive) moves the file writes to a background thread so that a recording
+    tee does not stall the receive loop on disk I/O; the file is complete when the ``with`` block
+    exits.  The bytes on disk are the same either way.
+    """
+
+    def __init__(self, outpath="blendtorch.mpkl", max_messages=100000, async_write=False):
         outpath = Path(outpath)
         outpath.parent.mkdir(parents=True, exist_ok=True)
         self.outpath = outpath
         self.capacity = max_messages
         self.file = None
+        self.async_write = async_write
+        self._queue = self._writer = self._error = None
         _logger.info(f"Recording configured for path {outpath}, max_messages {max_messages}.")
 
     def __enter__(self):
@@ -46,12 +52,29 @@ class FileRecorder:
         self.offsets = np.full(self.capacity, -1, dtype=np.int64)
         self.num_messages = 0
         self._pos = self._write_header()
+        if self.async_write:
+            import queue
+            import threading
+            self._queue = queue.Queue(maxsize=64)
+            self._writer = threading.Thread(target=self._drain, daemon=True, name="bt-recorder")
+            self._writer.start()
         return self
 
     def _write_header(self):
         blob = pickle.dumps(self.offsets, protocol=_HEADER_PROTOCOL)
         self.file.write(blob)
         return len(blob)
+
+    def _drain(self):
+        while True:
+            data = self._queue.get()
+            if data is None:
+                return
+            try:
+                if self._error is None:
+                    self.file.write(data)
+            except Exception as e:  # reported by __exit__
+                self._error = e
 
     def save(self, data, is_pickled=False):
         """Append one message; silently ignored once `max_messages` are stored (file.py:46)."""
@@ -61,16 +84,26 @@ class FileRecorder:
             data = pickle.dumps(data, protocol=_HEADER_PROTOCOL)
         self.offsets[self.num_messages] = self._pos
         self.num_messages += 1
-        self.file.write(data)
         self._pos += memoryview(data).nbytes
+        if self._queue is not None:
+            # the caller's buffer (a ZMQ frame) may be recycled after this call: keep a copy
+            self._queue.put(data if isinstance(data, bytes) else bytes(data))
+        else:
+            self.file.write(data)
 
     def __exit__(self, *args):
+        if self._queue is not None:
+            self._queue.put(None)
+            self._writer.join()
+            self._queue = self._writer = None
         # The header has a fixed length (the array shape never changes), so it is rewritten
         # in place with the final offsets (file.py:69-74).
         self.file.seek(0)
         self._write_header()
         self.file.close()
         self.file = None
+        if self._error is not None:
+            raise self._error
 
     @staticmethod
     def filename(prefix, worker_idx):

@@ -266,7 +266,7 @@ class DeviceLoader:
             torch.cuda.set_device(self.device)
             sock, poller = open_pull_socket(ctx, ds.addresses, ds.queue_size)
             if ds.record_path_prefix is not None:
-                rec = FileRecorder(FileRecorder.filename(ds.record_path_prefix, rid), ds.max_items)
+                rec = FileRecorder(FileRecorder.filename(ds.record_path_prefix, rid), ds.max_items, async_write=True)
                 rec.__enter__()
             holder = []
             try:

@@ -497,9 +497,19 @@ void copy_or_defer(uint8_t* dst, const uint8_t* src, uint64_t n, std::vector<Cop
 }  // namespace
 
 // Persistent worker threads for bulk copies (replay).  One job at a time; the caller works too.
+namespace {
+WorkPool* g_pool = nullptr;
+std::once_flag g_pool_atfork;
+}  // namespace
+
 WorkPool& WorkPool::get() {
-  static WorkPool* pool = new WorkPool();  // intentionally leaked: workers may outlive static destruction
-  return *pool;
+  // Leaked on purpose (workers may outlive static destruction).  Threads do not survive fork():
+  // a forked child (e.g. a DataLoader worker) starts over with a fresh pool.
+  std::call_once(g_pool_atfork, [] { pthread_atfork(nullptr, nullptr, [] { g_pool = nullptr; }); });
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!g_pool) g_pool = new WorkPool();
+  return *g_pool;
 }
 
 void WorkPool::worker(int index) {

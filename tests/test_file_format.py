@@ -97,3 +97,14 @@ def test_spans_point_at_messages(golden_dir):
         blob = ctypes.string_at(int(a), int(l))
         assert blob == bytes(r.raw(i))
         assert pickle.loads(blob)["frameid"] == i
+
+
+def test_async_recorder_writes_identical_files(golden_dir, tmp_path):
+    src = FileReader(golden_dir / "rec_small_00.btr")
+    for mode in (False, True):
+        with FileRecorder(tmp_path / ("m%d.btr" % mode), max_messages=8, async_write=mode) as rec:
+            for i in range(len(src)):
+                rec.save(src.raw(i), is_pickled=True)           # memoryviews, as the receive loop passes them
+            rec.save({"v": 1})
+    assert (tmp_path / "m0.btr").read_bytes() == (tmp_path / "m1.btr").read_bytes()
+    assert len(FileReader(tmp_path / "m1.btr")) == len(src) + 1
