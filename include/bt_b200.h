@@ -338,6 +338,35 @@ typedef struct bt_project_params {
 int bt_project_launch(const bt_project_params* p, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * K3: synthetic Cube-scene frame source on the GPU.
+ * Stands in for the draw + read-back of pkg_blender/blendtorch/btb/offscreen.py:76-92 in benchmarks
+ * and self-checks, without any graphics API: an edge-function rasteriser for boxes (12 triangles
+ * each), nearest-depth test, flat two-sided shading.  Corners are projected with K2's arithmetic
+ * (camera.py:84-136), so annotation corners projected by K2 lie on the rasterised silhouettes.
+ * Triangles with a corner at or behind the camera plane are dropped (no clipping).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct bt_raster_params {
+  const double* corners;  /* device [batch][ncubes][8][3] world coordinates; corner order (x,y,z) in
+                             {+1,-1}^3 with z fastest, then y, then x (the default-cube order) */
+  const double* view;     /* device [batch or 1][4][4] row-major */
+  const double* proj;     /* device [batch or 1][4][4] row-major */
+  int32_t batch, ncubes;  /* ncubes <= 32 */
+  int32_t view_per_frame, proj_per_frame;
+  int32_t height, width;
+  int32_t bottom_up;      /* 1: row 0 of the output is the bottom row (GL read-back order, the input
+                             K1's flip expects); 0: top row first */
+  float far_depth;        /* depth written where nothing was hit */
+  uint8_t background[4];  /* RGBA */
+  float light[3];         /* light direction in camera space (any length) */
+  int32_t reserved;
+  const uint8_t* colors;  /* optional device [ncubes][4] base colours; NULL = built-in palette */
+  uint8_t* image_out;     /* device [batch][height][width][4] uint8 RGBA */
+  float* depth_out;       /* optional device [batch][height][width] linear camera-space depth */
+} bt_raster_params;
+
+int bt_raster_launch(const bt_raster_params* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Small CUDA helpers so that callers without a CUDA binding can drive the path
  * (reference counterpart: none; the reference never touches the device inside the library).
  * ------------------------------------------------------------------------------------------ */

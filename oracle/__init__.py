@@ -28,4 +28,4 @@ Blender side, btt/file.py:63,72), numpy ndarray pickling, and
 `torch.utils.data.default_collate` (installed torch 2.11, collate.py:118-313).
 """
 
-from . import btr, camera, preprocess, stream, synth  # noqa: F401
+from . import btr, camera, preprocess, raster, stream, synth  # noqa: F401

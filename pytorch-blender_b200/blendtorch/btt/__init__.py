@@ -13,10 +13,11 @@ from . import native
 from .preprocess import Preprocess, preprocess_images
 from .camera import Camera, Projection
 from .loader import DeviceLoader, shard
+from .raster import render_cubes
 from .publisher import DataPublisher
 
 __version__ = "0.2.0+b200.1"
 
 __all__ = ["RemoteIterableDataset", "FileDataset", "SingleFileDataset", "FileRecorder", "FileReader",
-           "DeviceLoader", "Preprocess", "preprocess_images", "Camera", "Projection", "DataPublisher", "shard",
+           "DeviceLoader", "Preprocess", "preprocess_images", "Camera", "Projection", "DataPublisher", "shard", "render_cubes",
            "DEFAULT_TIMEOUTMS", "native"]

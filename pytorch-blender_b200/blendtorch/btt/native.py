@@ -144,7 +144,7 @@ EXPORTS = ["bt_last_error", "bt_abi_version", "bt_scan_message", "bt_schema_crea
            "bt_shm_create", "bt_shm_attach", "bt_shm_close", "bt_shm_nslots", "bt_shm_slot_bytes",
            "bt_shm_slot_ptr", "bt_shm_acquire", "bt_shm_release",
            "bt_build_gamma_lut", "bt_preprocess_scratch_bytes", "bt_preprocess_launch",
-           "bt_preprocess_last_variant", "bt_preprocess_stats_static", "bt_project_launch", "bt_device_count", "bt_measure_h2d"]
+           "bt_preprocess_last_variant", "bt_preprocess_stats_static", "bt_project_launch", "bt_raster_launch", "bt_device_count", "bt_measure_h2d"]
 
 
 def last_error():

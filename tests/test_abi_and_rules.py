@@ -38,13 +38,17 @@ def test_struct_sizes_match_header(tmp_path):
     """ctypes mirrors vs. the C compiler's view of the header."""
     from blendtorch.btt import native as N
     src = tmp_path / "sz.c"
-    src.write_text('#include <stdio.h>\n#include "bt_b200.h"\nint main(){printf("%zu %zu %zu %zu\\n",'
-                   'sizeof(bt_field),sizeof(bt_column),sizeof(bt_preprocess_params),sizeof(bt_project_params));return 0;}\n')
+    src.write_text('#include <stdio.h>\n#include "bt_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu\\n",'
+                   'sizeof(bt_field),sizeof(bt_column),sizeof(bt_preprocess_params),sizeof(bt_project_params),'
+                   'sizeof(bt_raster_params),sizeof(bt_zmq_api));return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", str(ROOT / "include"), str(src), "-o", str(exe)], check=True)
     sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True).stdout.split()]
+    from blendtorch.btt.raster import RasterParams
+    from blendtorch.btt.rx import ZmqApi
     assert sizes == [ctypes.sizeof(N.Field), ctypes.sizeof(N.Column),
-                     ctypes.sizeof(N.PreprocessParams), ctypes.sizeof(N.ProjectParams)]
+                     ctypes.sizeof(N.PreprocessParams), ctypes.sizeof(N.ProjectParams),
+                     ctypes.sizeof(RasterParams), ctypes.sizeof(ZmqApi)]
 
 
 def test_error_reporting():
