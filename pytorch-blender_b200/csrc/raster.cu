@@ -64,6 +64,8 @@ __global__ void __launch_bounds__(kTile* kTile) k3_raster(bt_raster_params p) {
   __shared__ unsigned char ok[kMaxCubes * 8];
   __shared__ Tri tris[kMaxCubes * kTrisPerCube];
   __shared__ unsigned char live[kMaxCubes * kTrisPerCube];
+  __shared__ unsigned short order[kMaxCubes * kTrisPerCube];
+  __shared__ int nlive;
 
   const int b = blockIdx.z;
   const int tid = threadIdx.y * kTile + threadIdx.x;
@@ -142,6 +144,20 @@ __global__ void __launch_bounds__(kTile* kTile) k3_raster(bt_raster_params p) {
     live[t] = 1;
   }
   __syncthreads();
+  // order-preserving compaction of the triangles that can touch this tile (most tiles see a few
+  // of the 12*ncubes): warp 0 scans the flags 32 at a time with ballots
+  if (tid < 32) {
+    int base = 0;
+    for (int t0 = 0; t0 < p.ncubes * kTrisPerCube; t0 += 32) {
+      const int t = t0 + tid;
+      const bool on = t < p.ncubes * kTrisPerCube && live[t];
+      const unsigned m = __ballot_sync(0xffffffffu, on);
+      if (on) order[base + __popc(m & ((1u << tid) - 1u))] = (unsigned short)t;
+      base += __popc(m);
+    }
+    if (tid == 0) nlive = base;
+  }
+  __syncthreads();
 
   // phase C: one pixel per thread, nearest depth wins; ties keep the lower triangle index
   const int px = blockIdx.x * kTile + threadIdx.x, py = blockIdx.y * kTile + threadIdx.y;
@@ -151,9 +167,8 @@ __global__ void __launch_bounds__(kTile* kTile) k3_raster(bt_raster_params p) {
   unsigned int color = (unsigned int)p.background[0] | ((unsigned int)p.background[1] << 8) |
                        ((unsigned int)p.background[2] << 16) | ((unsigned int)p.background[3] << 24);
   {
-    for (int t = 0; t < p.ncubes * kTrisPerCube; ++t) {
-      if (!live[t]) continue;
-      const Tri& tr = tris[t];
+    for (int j = 0; j < nlive; ++j) {
+      const Tri& tr = tris[order[j]];
       float w0 = edge(tr.x1, tr.y1, tr.x2, tr.y2, fx, fy);
       float w1 = edge(tr.x2, tr.y2, tr.x0, tr.y0, fx, fy);
       float w2 = edge(tr.x0, tr.y0, tr.x1, tr.y1, fx, fy);
