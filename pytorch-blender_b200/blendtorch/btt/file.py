@@ -20,6 +20,7 @@ import io
 import logging
 import mmap
 import pickle
+import threading
 from pathlib import Path
 
 import numpy as np
@@ -27,6 +28,7 @@ import numpy as np
 _logger = logging.getLogger("blendtorch")
 
 _HEADER_PROTOCOL = 3  # file.py:63,72 -- readable by Blender's Python 3.7
+_map_lock = threading.Lock()
 
 
 class FileRecorder:
@@ -136,20 +138,25 @@ class FileReader:
 
     # ---- zero-unpickle access (new) -----------------------------------------------------
     def _ensure_map(self):
-        if self._map is None:
+        if self._map is not None:
+            return self._map
+        with _map_lock:  # several producer threads may ask at once; exactly one mapping may win
+            if self._map is not None:
+                return self._map
             with io.open(self.path, "rb") as f:
                 # pre-fault the mapping: replay touches every page, and a page fault per 4 KiB
                 # in the copy loop would cap it at a few GB/s
                 flags = mmap.MAP_SHARED | getattr(mmap, "MAP_POPULATE", 0)
-                self._map = mmap.mmap(f.fileno(), 0, flags=flags, prot=mmap.PROT_READ)
-            size = len(self._map)
+                new_map = mmap.mmap(f.fileno(), 0, flags=flags, prot=mmap.PROT_READ)
+            size = len(new_map)
             ends = np.empty(len(self.offsets), dtype=np.int64)
             if len(ends):
                 ends[:-1] = self.offsets[1:]
                 ends[-1] = size
             self._ends = ends
             # base address of the mapping, for handing spans to the native layer
-            self._base = np.frombuffer(self._map, dtype=np.uint8).ctypes.data if size else 0
+            self._base = np.frombuffer(new_map, dtype=np.uint8).ctypes.data if size else 0
+            self._map = new_map   # published last: readers of _map see _ends/_base complete
         return self._map
 
     def raw(self, idx):

@@ -133,9 +133,10 @@ class DeviceLoader:
         the uint8 frames as they are -- exactly default_collate's output, on the device.
     project: a `Projection` or list of them: world points carried by the messages are projected to
         pixels (and per-object boxes) on the GPU, one K2 launch per batch.
-    num_receivers: receiver threads for streams; each owns a PULL socket connected to all
+    num_receivers: receiver threads for streams (default 1); each owns a PULL socket connected to all
         addresses and takes ``max_items // num_receivers`` items, like the reference's DataLoader
-        workers (dataset.py:80-85,97).
+        workers (dataset.py:80-85,97).  For replay: producer threads (default 2) that fill alternate
+        batches; the sampler's batch order is preserved.
     ring_depth: pinned slots per receiver.  prefetch: finished batches queued ahead of the consumer.
     ingest_threads: host threads `bt_schema_ingest_many` uses per replay batch.
     io_threads: ZMQ I/O threads per receiver; a receiver's connections (one per publisher) are
@@ -145,7 +146,7 @@ class DeviceLoader:
     """
 
     def __init__(self, dataset, batch_size=1, shuffle=False, drop_last=False, device="cuda",
-                 preprocess=None, num_receivers=1, ring_depth=3, prefetch=2, ingest_threads=4,
+                 preprocess=None, num_receivers=None, ring_depth=3, prefetch=2, ingest_threads=4,
                  seed=0, keep_raw=False, io_threads=1, project=None):
         self.dataset = dataset
         self.batch_size = int(batch_size)
@@ -168,7 +169,8 @@ class DeviceLoader:
         elif not isinstance(project, (list, tuple)):
             project = [project]
         self.projections = tuple(project)
-        self.num_receivers = max(1, int(num_receivers))
+        self._num_receivers_arg = num_receivers
+        self.num_receivers = max(1, int(num_receivers or 1))
         self.ring_depth, self.prefetch = int(ring_depth), int(prefetch)
         self.ingest_threads = int(ingest_threads)
         self.seed, self.keep_raw = seed, keep_raw
@@ -425,7 +427,8 @@ class DeviceLoader:
             readers = [d.reader for d in ds.datasets]
             custom = ds.has_custom_item()
             B = self.batch_size
-            for start in range(0, len(order), B):
+            n_prod = self._replay_producers()
+            for start in range(rid * B, len(order), B * n_prod):   # producer `rid` takes batches rid, rid+n, ...
                 if stop.is_set():
                     return
                 idx = order[start:start + B]
@@ -467,24 +470,47 @@ class DeviceLoader:
             out_q.put(_DONE)
 
     # ---- consumer ---------------------------------------------------------------------------
+    def _replay_producers(self):
+        # two producers by default: one fills a pinned slot while the other submits its batch
+        n = 2 if self._num_receivers_arg is None else self.num_receivers
+        return max(1, min(n, 8))
+
     def __iter__(self):
-        out_q = queue.Queue(maxsize=max(1, self.prefetch))
         stop = threading.Event()
         if self._mode == "stream":
             n_prod, target = self.num_receivers, self._stream_producer
+            queues = [queue.Queue(maxsize=max(1, self.prefetch))] * n_prod      # one shared queue: unordered
         else:
-            n_prod, target = 1, self._replay_producer
-        threads = [threading.Thread(target=target, args=(r, out_q, stop), daemon=True, name="bt-recv-%d" % r)
+            # Replay keeps the sampler's order: producer r makes batches r, r+n, ... into its own
+            # queue and the consumer reads the queues round-robin.
+            n_prod, target = self._replay_producers(), self._replay_producer
+            queues = [queue.Queue(maxsize=max(1, self.prefetch)) for _ in range(n_prod)]
+        threads = [threading.Thread(target=target, args=(r, queues[r], stop), daemon=True, name="bt-recv-%d" % r)
                    for r in range(n_prod)]
         self._epoch += 1
         for t in threads:
             t.start()
-        live = n_prod
+        ordered = self._mode != "stream"
+        alive = [True] * n_prod
+        turn = 0
         try:
-            while live:
-                item = out_q.get()
+            while any(alive):
+                if ordered:
+                    if not alive[turn]:
+                        break                      # the producer whose turn it is has no more batches
+                    item = queues[turn].get()
+                else:
+                    item = queues[0].get()
                 if item is _DONE:
-                    live -= 1
+                    if ordered:
+                        alive[turn] = False
+                        # a finished producer ends the epoch only when its turn comes round again;
+                        # later producers may still hold the batches in between
+                        turn = (turn + 1) % n_prod
+                        if not any(alive):
+                            break
+                        continue
+                    alive[alive.index(True)] = False
                     continue
                 if isinstance(item, BaseException):
                     raise item
@@ -496,13 +522,15 @@ class DeviceLoader:
                 self.stats["batches"] += 1
                 self.stats["items"] += len(batch["btid"]) if "btid" in batch else next((len(v) for v in batch.values()), 0)
                 yield batch
+                if ordered:
+                    turn = (turn + 1) % n_prod
         finally:
             stop.set()
             # unblock producers waiting on a full queue, then let them finish cleanly
-            for t in threads:
+            for t, q in zip(threads, queues):
                 while t.is_alive():
                     try:
-                        out_q.get_nowait()
+                        q.get_nowait()
                     except queue.Empty:
                         pass
                     t.join(timeout=0.05)

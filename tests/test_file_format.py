@@ -108,3 +108,25 @@ def test_async_recorder_writes_identical_files(golden_dir, tmp_path):
             rec.save({"v": 1})
     assert (tmp_path / "m0.btr").read_bytes() == (tmp_path / "m1.btr").read_bytes()
     assert len(FileReader(tmp_path / "m1.btr")) == len(src) + 1
+
+
+def test_concurrent_first_use_of_the_mapping(golden_dir):
+    """Several replay producers may touch a reader at once; its lazily created mapping must be set up once."""
+    import ctypes
+    import threading
+    for _ in range(20):
+        r = FileReader(golden_dir / "rec_small_00.btr")
+        out, errs = [], []
+
+        def work():
+            try:
+                a, l = r.spans([0, 5])
+                out.append((int(a[1]), ctypes.string_at(int(a[1]), int(l[1]))))
+            except Exception as e:
+                errs.append(e)
+
+        ts = [threading.Thread(target=work) for _ in range(8)]
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+        assert not errs and len({x[0] for x in out}) == 1 and len({x[1] for x in out}) == 1
+        r.close()

@@ -238,3 +238,20 @@ def test_config3_depth_and_projection_in_loader(tmp_path):
     again = [b["frameid"].tolist() for b in dl]
     assert sum(len(x) for x in again) == 10
     dl.close()
+
+
+@pytest.mark.parametrize("producers", [2, 3, 5])
+def test_replay_with_several_producers_keeps_order(golden_dir, producers):
+    ds = btt.FileDataset(str(golden_dir / "rec_small"))
+    one = [(b["btid"].tolist(), b["frameid"].tolist(), b["image"].cpu()) for b in
+           btt.DeviceLoader(ds, batch_size=2, device=DEV, shuffle=True, seed=5)]
+    dl = btt.DeviceLoader(ds, batch_size=2, device=DEV, shuffle=True, seed=5, num_receivers=producers)
+    many = [(b["btid"].tolist(), b["frameid"].tolist(), b["image"].cpu()) for b in dl]
+    assert len(one) == len(many) == 6
+    for a, b in zip(one, many):
+        assert a[0] == b[0] and a[1] == b[1] and torch.equal(a[2], b[2])
+    # drop_last and a second epoch
+    dl = btt.DeviceLoader(ds, batch_size=4, device=DEV, drop_last=True, num_receivers=producers)
+    assert [len(b["frameid"]) for b in dl] == [4, 4]
+    assert [b["frameid"].tolist() for b in dl] == [[0, 1, 2, 3], [4, 5, 0, 1]]
+    dl.close()

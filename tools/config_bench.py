@@ -43,7 +43,7 @@ def timed(dl, warm, steps, after=None):
     return n, dt
 
 
-def replay_case(name, config, h, w, batch, files, frames, threads, steps, spec, extra=None, shuffle=True):
+def replay_case(name, config, h, w, batch, files, frames, threads, steps, spec, extra=None, shuffle=True, producers=1):
     d = tempfile.mkdtemp(prefix="btrec_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
     try:
         prefix = d + "/rec"
@@ -51,7 +51,7 @@ def replay_case(name, config, h, w, batch, files, frames, threads, steps, spec, 
         ds = btt.FileDataset(prefix)
         per_item = os.path.getsize(ds.filenames[0]) / frames
         dl = btt.DeviceLoader(ds, batch_size=batch, shuffle=shuffle, device=DEV, preprocess=spec, ingest_threads=threads,
-                              ring_depth=3, prefetch=3, drop_last=True)
+                              ring_depth=3, prefetch=3, drop_last=True, num_receivers=producers)
         epochs = max(1, -(-(steps + 3) * batch // len(ds)))
 
         class Multi:
@@ -60,7 +60,7 @@ def replay_case(name, config, h, w, batch, files, frames, threads, steps, spec, 
                     yield from dl
         n, dt = timed(Multi(), 3, steps, extra)
         return {"case": name, "images_per_s": n / dt, "GBps_h2d": n / dt * per_item / 1e9, "batch": batch,
-                "ingest_threads": threads, "frames": [h, w]}
+                "ingest_threads": threads, "producers": producers, "frames": [h, w]}
     finally:
         shutil.rmtree(d, ignore_errors=True)
 
@@ -85,8 +85,8 @@ def main():
     torch.cuda.set_device(0)
     spec = btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5)
     out = []
-    for th in (1, 4, 8):
-        out.append(replay_case("C1 replay 640x480 b8 (.btr in page cache)", 1, 480, 640, 8, 4, 256, th, 400, spec))
+    for th, pr in ((1, 1), (4, 1), (4, 2), (4, 3), (2, 4)):
+        out.append(replay_case("C1 replay 640x480 b8 (.btr in page cache)", 1, 480, 640, 8, 4, 256, th, 400, spec, producers=pr))
     from oracle import camera as ocam
     shape = (1080, 1920)
     cam = btt.Camera(ocam.view_looking_down_z(0.0), ocam.blender_perspective(shape, lens=35.0), shape, device=DEV)
