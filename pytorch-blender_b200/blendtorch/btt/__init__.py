@@ -1,8 +1,8 @@
 """blendtorch.btt -- B200-native ingest path with the reference's surface.
 
 Same public names as pkg_pytorch/blendtorch/btt/__init__.py for the ingest path
-(`RemoteIterableDataset`, `FileDataset`, `FileRecorder`, `FileReader`); the control plane of the
-reference (launcher, duplex channel, gym environments) is out of scope here and not provided.
+(`RemoteIterableDataset`, `FileDataset`, `FileRecorder`, `FileReader`); the launcher and the gym
+environments of the reference are out of scope here and not provided (`DuplexChannel` is).
 New, additive names: `DeviceLoader`, `Preprocess`, `preprocess_images`, `Camera`, `DataPublisher`,
 `shard`.
 """
@@ -15,9 +15,10 @@ from .camera import Camera, Projection
 from .loader import DeviceLoader, shard
 from .raster import render_cubes
 from .publisher import DataPublisher
+from .duplex import DuplexChannel
 
 __version__ = "0.2.0+b200.1"
 
 __all__ = ["RemoteIterableDataset", "FileDataset", "SingleFileDataset", "FileRecorder", "FileReader",
-           "DeviceLoader", "Preprocess", "preprocess_images", "Camera", "Projection", "DataPublisher", "shard", "render_cubes",
+           "DeviceLoader", "Preprocess", "preprocess_images", "Camera", "Projection", "DataPublisher", "DuplexChannel", "shard", "render_cubes",
            "DEFAULT_TIMEOUTMS", "native"]
