@@ -308,7 +308,7 @@ def large_batch_probe(torch, btt, dev, spec):
     return B2 * H2 * W2 * C * 5 / sec / 1e9, sec
 
 
-def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_threads=1, shm_slots=0):
+def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_threads=1, shm_slots=0, rx="auto"):
     """Public API with host buffers: publishers -> DeviceLoader -> device batch (+ stats read back)."""
     addrs, procs = spawn_publishers("blendtorch.btt.synthetic", PUBLISHERS, transport, tag="r%s" % os.environ.get("RANK", "0"),
                                     extra=("--shm-slots", str(shm_slots)) if shm_slots else ())
@@ -318,7 +318,7 @@ def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_th
         ds = btt.RemoteIterableDataset(addrs, max_items=per_recv * receivers + 0, timeoutms=60000)
         spec = btt.Preprocess(key="image", flip=True, gamma=GAMMA, mean=MEAN, std=STD, stats=True)
         dl = btt.DeviceLoader(ds, batch_size=BATCH, device=dev, preprocess=spec, num_receivers=receivers,
-                              ring_depth=4, prefetch=4, io_threads=io_threads)
+                              ring_depth=4, prefetch=4, io_threads=io_threads, transport=rx)
         it = iter(dl)
         h2d = d2h = 0
         for _ in range(warmup):

@@ -214,6 +214,26 @@ int bt_rx_fill(bt_rx* rx, bt_ring* ring, int slot, const bt_schema* schema, int 
 int bt_rx_release_queued(bt_rx* rx, int* n_released);
 
 /* ------------------------------------------------------------------------------------------
+ * Direct receiver: a minimal ZMTP 3 PULL endpoint (tcp:// and ipc://) that needs no libzmq and lands
+ * array payloads straight from the kernel socket in the staging slot -- one CPU copy per payload byte
+ * on the consumer side.  Replaces `socket.recv()` + `pickle.loads` of
+ * pkg_pytorch/blendtorch/btt/dataset.py:98-106 against unmodified PUSH publishers
+ * (pkg_blender/blendtorch/btb/publisher.py:21-27).  Same calling contract as bt_rx_*.
+ * Like the reference's socket it connects to every address given (dataset.py:77-78), takes messages
+ * fairly from whichever publisher has one, and retries publishers that are not up yet.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct bt_pull bt_pull;
+
+int bt_pull_create(bt_pull** out);
+int bt_pull_connect(bt_pull* q, const char* address);   /* "tcp://host:port" or "ipc://path" */
+int bt_pull_destroy(bt_pull* q);
+int bt_pull_recv(bt_pull* q, int timeout_ms);            /* hold one whole message (BT_OK) or BT_E_TIMEOUT */
+int bt_pull_pending(bt_pull* q, const uint8_t** data, uint64_t* len);
+int bt_pull_drop(bt_pull* q);
+int bt_pull_fill(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, int first_item, int max_items,
+                 int slice_ms, int* n_done);
+
+/* ------------------------------------------------------------------------------------------
  * Shared-memory wire (opt-in, co-located producers).
  * No counterpart in the reference, whose only transport is the pickled ZMQ message
  * (btb/publisher.py:43).  A producer writes each large array into a slot of a POSIX shared-memory

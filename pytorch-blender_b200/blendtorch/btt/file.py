@@ -123,18 +123,20 @@ class FileReader:
         self._unpickler = None
         self._map = None
         self._ends = None
+        self._lock = threading.Lock()
 
     def __len__(self):
         return len(self.offsets)
 
     def __getitem__(self, idx):
         """Unpickle message `idx` (the reference's per-item path)."""
-        if self._file is None:
-            # opened lazily so that forked DataLoader workers get their own descriptor
-            self._file = io.open(self.path, "rb", buffering=0)
-            self._unpickler = pickle.Unpickler(self._file)
-        self._file.seek(self.offsets[idx])
-        return self._unpickler.load()
+        with self._lock:  # seek + load share one descriptor; replay producers are threads
+            if self._file is None:
+                # opened lazily so that forked DataLoader workers get their own descriptor
+                self._file = io.open(self.path, "rb", buffering=0)
+                self._unpickler = pickle.Unpickler(self._file)
+            self._file.seek(self.offsets[idx])
+            return self._unpickler.load()
 
     # ---- zero-unpickle access (new) -----------------------------------------------------
     def _ensure_map(self):
@@ -191,7 +193,12 @@ class FileReader:
         d = self.__dict__.copy()
         d["_file"] = d["_unpickler"] = d["_map"] = d["_ends"] = None
         d.pop("_base", None)
+        d.pop("_lock", None)
         return d
+
+    def __setstate__(self, d):
+        self.__dict__.update(d)
+        self._lock = threading.Lock()
 
     @staticmethod
     def read_offsets(fname):

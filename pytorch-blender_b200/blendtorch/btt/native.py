@@ -108,6 +108,13 @@ def _load():
         "bt_rx_drop": (i32, [vp]),
         "bt_rx_fill": (i32, [vp, vp, i32, vp, i32, i32, i32, C.POINTER(i32)]),
         "bt_rx_release_queued": (i32, [vp, C.POINTER(i32)]),
+        "bt_pull_create": (i32, [C.POINTER(vp)]),
+        "bt_pull_connect": (i32, [vp, C.c_char_p]),
+        "bt_pull_destroy": (i32, [vp]),
+        "bt_pull_recv": (i32, [vp, i32]),
+        "bt_pull_pending": (i32, [vp, C.POINTER(vp), C.POINTER(u64)]),
+        "bt_pull_drop": (i32, [vp]),
+        "bt_pull_fill": (i32, [vp, vp, i32, vp, i32, i32, i32, C.POINTER(i32)]),
         "bt_shm_create": (i32, [C.c_char_p, u64, i32, C.POINTER(vp)]),
         "bt_shm_attach": (i32, [C.c_char_p, i32, C.POINTER(vp)]),
         "bt_shm_close": (i32, [vp]),
@@ -141,6 +148,8 @@ EXPORTS = ["bt_last_error", "bt_abi_version", "bt_scan_message", "bt_schema_crea
            "bt_ring_ingest", "bt_ring_submit_batch", "bt_ring_spill", "bt_ring_reap",
            "bt_rx_create", "bt_rx_destroy", "bt_rx_recv", "bt_rx_pending", "bt_rx_drop", "bt_rx_fill",
            "bt_rx_release_queued",
+           "bt_pull_create", "bt_pull_connect", "bt_pull_destroy", "bt_pull_recv", "bt_pull_pending",
+           "bt_pull_drop", "bt_pull_fill",
            "bt_shm_create", "bt_shm_attach", "bt_shm_close", "bt_shm_nslots", "bt_shm_slot_bytes",
            "bt_shm_slot_ptr", "bt_shm_acquire", "bt_shm_release",
            "bt_build_gamma_lut", "bt_preprocess_scratch_bytes", "bt_preprocess_launch",

@@ -93,3 +93,59 @@ class Receiver:
             self.close()
         except Exception:
             pass
+
+
+def direct_capable(addresses):
+    """True when every address is one the direct receiver can speak to (tcp:// or ipc://)."""
+    return all(isinstance(a, str) and (a.startswith("tcp://") or a.startswith("ipc://")) for a in addresses)
+
+
+class DirectReceiver:
+    """Same interface as `Receiver`, without libzmq: a ZMTP 3 PULL endpoint in C (``bt_pull_*``) whose
+    array payloads go from the kernel socket straight into the staging slot."""
+
+    def __init__(self, addresses):
+        self.handle = C.c_void_p()
+        N.check(N.lib.bt_pull_create(C.byref(self.handle)))
+        try:
+            for a in addresses:
+                N.check(N.lib.bt_pull_connect(self.handle, a.encode()))
+        except Exception:
+            self.close()
+            raise
+
+    def recv(self, timeout_ms):
+        rc = N.lib.bt_pull_recv(self.handle, int(timeout_ms))
+        if rc == N.BT_E_TIMEOUT:
+            return False
+        N.check(rc)
+        return True
+
+    def pending(self):
+        p, n = C.c_void_p(), C.c_uint64()
+        N.check(N.lib.bt_pull_pending(self.handle, C.byref(p), C.byref(n)))
+        return memoryview((C.c_uint8 * n.value).from_address(p.value)).cast("B")
+
+    def drop(self):
+        N.check(N.lib.bt_pull_drop(self.handle))
+
+    def fill(self, ring, slot, schema, first_item, max_items, slice_ms=100):
+        n = C.c_int(0)
+        rc = N.lib.bt_pull_fill(self.handle, ring.handle, slot, schema.handle, first_item, max_items, slice_ms, C.byref(n))
+        if rc not in (N.BT_OK, N.BT_E_TIMEOUT, N.BT_E_UNSUPPORTED, N.BT_E_SCHEMA):
+            N.check(rc)
+        return rc, n.value
+
+    def release_queued(self):
+        return 0  # nothing is queued in user space: unread messages stay with their publishers
+
+    def close(self):
+        if self.handle:
+            N.lib.bt_pull_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

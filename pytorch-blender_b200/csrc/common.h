@@ -102,6 +102,18 @@ class WorkPool {
   uint64_t generation_ = 0;
 };
 
+// Streaming scan of a message that arrives in pieces (zmtp.cpp).  stream_run returns BT_OK when the
+// pickle's STOP was reached, BT_E_TRUNCATED when more bytes are needed (call again with the grown
+// buffer), 1 when the VM stands on a large payload that is still on the wire: stream_big_target
+// says which schema column it belongs to (after checking dtype/shape/size), the receiver lands
+// stream_big_len() bytes there, cuts the buffer back to stream_pos() and calls stream_run again.
+void stream_begin();
+int stream_run(const uint8_t* buf, uint64_t n);
+uint64_t stream_pos();
+uint64_t stream_big_len();
+int stream_big_target(const bt_schema* schema, int* column);
+int stream_fields(const uint8_t* buf, std::vector<bt_field>& out);
+
 // Process-wide registry of attached segments (shm.cu).
 int shm_attach_cached(const char* name, size_t name_len, int device, bt_shm** out);
 

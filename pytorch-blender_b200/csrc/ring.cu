@@ -35,6 +35,19 @@ void release_refs(std::vector<bt::PendingRef>& v) {
 }
 }  // namespace
 
+namespace bt {
+
+uint8_t* ring_slot_base(bt_ring* r, int slot) { return r->base + r->slot_bytes * (uint64_t)slot; }
+
+int ring_place(bt_ring* r, int slot, const bt_schema* s, int item, const uint8_t* msg, const std::vector<bt_field>& f) {
+  const size_t before = r->pending[slot].size();
+  int rc = place_fields(s, ring_slot_base(r, slot), item, msg, f, r->pinned ? &r->pending[slot] : nullptr, r->device);
+  if (rc != BT_OK) r->pending[slot].resize(before);  // the caller's compatibility decode fetches and releases them
+  return rc;
+}
+
+}  // namespace bt
+
 extern "C" {
 
 int bt_ring_create(int device, uint64_t slot_bytes, int depth, bt_ring** out) {

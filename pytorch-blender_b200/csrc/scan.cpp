@@ -24,6 +24,10 @@ std::string& last_error_ref() {
 
 namespace {
 
+constexpr uint64_t kBigPayload = 16 * 1024;          // smaller payloads are simply buffered
+constexpr uint64_t kExternalBase = ~0ull - 1024;     // N_BYTES.off >= this: payload #(off - base) is external
+constexpr int kScanBig = 1;
+
 enum NK : uint8_t {
   N_NONE, N_BOOL, N_INT, N_FLOAT, N_STR, N_BYTES, N_TUPLE, N_LIST, N_DICT, N_GLOBAL, N_OBJ, N_BIGINT
 };
@@ -47,11 +51,19 @@ struct Scanner {
   std::vector<std::vector<int>> kidpool;
   int kidpool_used = 0;
   int root = -1;
+  // streaming mode (zmtp.cpp): the buffer grows between calls of run(); an opcode that does not
+  // fit yet is re-decoded later, and a large payload that is still on the wire becomes an
+  // "external" span that the receiver lands directly in its final place.
+  bool streaming = false;
+  uint64_t op_start = 0;
+  uint64_t big_len = 0;
+  int n_external = 0;
 
   void reset(const uint8_t* buf, uint64_t len) {
     p = buf; n = len; pos = 0;
     nodes.clear(); stack.clear(); marks.clear(); memo.clear();
     memo_count = 0; kidpool_used = 0; root = -1;
+    streaming = false; op_start = 0; big_len = 0; n_external = 0;
   }
   int new_node(NK k) {
     nodes.emplace_back();
@@ -79,11 +91,13 @@ struct Scanner {
   int run();
 };
 
-#define NEED(k) do { if (!need(k)) return fail(BT_E_TRUNCATED, "pickle truncated at byte %llu", (unsigned long long)pos); } while (0)
+#define NEED(k) do { if (!need(k)) { if (streaming) { pos = op_start; return BT_E_TRUNCATED; } \
+    return fail(BT_E_TRUNCATED, "pickle truncated at byte %llu", (unsigned long long)pos); } } while (0)
 #define STACK(k) do { if (stack.size() < (size_t)(k)) return fail(BT_E_UNSUPPORTED, "pickle stack underflow at byte %llu", (unsigned long long)pos); } while (0)
 
 int Scanner::run() {
   while (true) {
+    op_start = pos;
     NEED(1);
     uint8_t op = p[pos++];
     switch (op) {
@@ -145,6 +159,16 @@ int Scanner::run() {
         int w = op == 'B' ? 4 : (op == 'C' ? 1 : 8);
         NEED(w);
         uint64_t l = le(w);
+        if (streaming && l >= kBigPayload && !need(l)) {
+          // the payload is (mostly) still on the wire: hand it to the receiver as an external span
+          int s = new_node(N_BYTES);
+          nodes[s].off = kExternalBase + (uint64_t)n_external;
+          nodes[s].len = l;
+          stack.push_back(s);
+          big_len = l;
+          ++n_external;
+          return kScanBig;  // `pos` stays at the first payload byte
+        }
         NEED(l);
         int s = new_node(N_BYTES);
         nodes[s].off = pos; nodes[s].len = l;
@@ -446,13 +470,9 @@ Scanner& tls_scanner() {
 
 }  // namespace
 
-// Scan into the thread-local scanner and describe top-level dict entries.
-int scan_fields(const uint8_t* msg, uint64_t len, std::vector<bt_field>& out) {
-  if (!msg && len) return fail(BT_E_INVALID, "null message");
-  Scanner& s = tls_scanner();
-  s.reset(msg, len);
-  int rc = s.run();
-  if (rc != BT_OK) return rc;
+namespace {
+// Describe the top-level dict entries of a finished scan.
+int collect_fields(const Scanner& s, const uint8_t* msg, std::vector<bt_field>& out) {
   const Node& r = s.nodes[s.root];
   if (r.k != N_DICT) return fail(BT_E_UNSUPPORTED, "top-level object is not a dict");
   const std::vector<int>& k = s.kidpool[r.kids];
@@ -471,6 +491,74 @@ int scan_fields(const uint8_t* msg, uint64_t len, std::vector<bt_field>& out) {
     classify(s, k[i + 1], f);
   }
   return BT_OK;
+}
+
+thread_local std::vector<int> g_ext_cols;  // streaming: column each external payload was landed in
+}  // namespace
+
+// Scan into the thread-local scanner and describe top-level dict entries.
+int scan_fields(const uint8_t* msg, uint64_t len, std::vector<bt_field>& out) {
+  if (!msg && len) return fail(BT_E_INVALID, "null message");
+  Scanner& s = tls_scanner();
+  s.reset(msg, len);
+  g_ext_cols.clear();
+  int rc = s.run();
+  if (rc != BT_OK) return rc;
+  return collect_fields(s, msg, out);
+}
+
+// ---- streaming scan: the message arrives in pieces, large payloads never enter the buffer -------
+void stream_begin() {
+  Scanner& s = tls_scanner();
+  s.reset(nullptr, 0);
+  s.streaming = true;
+  g_ext_cols.clear();
+}
+
+int stream_run(const uint8_t* buf, uint64_t n) {
+  Scanner& s = tls_scanner();
+  s.p = buf;
+  s.n = n;
+  return s.run();
+}
+
+uint64_t stream_pos() { return tls_scanner().pos; }
+uint64_t stream_big_len() { return tls_scanner().big_len; }
+
+int stream_big_target(const bt_schema* schema, int* column) {
+  // The VM stopped on the raw-data bytes of an ndarray state tuple:
+  //   ... key, <_reconstruct obj>, MARK, version, shape, dtype, is_fortran, <external bytes>
+  const Scanner& s = tls_scanner();
+  if (s.marks.empty()) return BT_E_UNSUPPORTED;
+  const int m = s.marks.back();
+  if (m < 2 || (int)s.stack.size() - m != 5) return BT_E_UNSUPPORTED;
+  const Node& owner = s.nodes[s.stack[m - 1]];
+  const Node& key = s.nodes[s.stack[m - 2]];
+  if (owner.k != N_OBJ || owner.callable < 0 || key.k != N_STR || key.len >= BT_MAX_KEY) return BT_E_UNSUPPORTED;
+  if (!global_is(s, s.nodes[owner.callable], "numpy.core.multiarray", "numpy._core.multiarray", "_reconstruct"))
+    return BT_E_UNSUPPORTED;
+  bt_field f;
+  memset(&f, 0, sizeof f);
+  if (!parse_shape(s, s.stack[m + 1], &f)) return BT_E_UNSUPPORTED;
+  const int dt = parse_dtype(s, s.stack[m + 2]);
+  const Node& fo = s.nodes[s.stack[m + 3]];
+  if (dt < 0 || fo.k != N_BOOL || (fo.i && f.ndim >= 2)) return BT_E_UNSUPPORTED;
+  f.dtype = dt;
+  for (size_t ci = 0; ci < schema->cols.size(); ++ci) {
+    const bt_column& c = schema->cols[ci];
+    if (strlen(c.key) != key.len || memcmp(c.key, s.p + key.off, key.len) != 0) continue;
+    if (c.kind != BT_KIND_NDARRAY || c.dtype != dt || c.ndim != f.ndim ||
+        memcmp(c.shape, f.shape, sizeof(int64_t) * c.ndim) != 0 || c.item_bytes != s.big_len)
+      return BT_E_SCHEMA;
+    *column = (int)ci;
+    g_ext_cols.push_back((int)ci);
+    return BT_OK;
+  }
+  return BT_E_SCHEMA;
+}
+
+int stream_fields(const uint8_t* buf, std::vector<bt_field>& out) {
+  return collect_fields(tls_scanner(), buf, out);
 }
 
 std::vector<bt_field>& tls_fields() {
@@ -579,6 +667,12 @@ int place_fields(const bt_schema* s, uint8_t* base, int item, const uint8_t* msg
             memcmp(fi->shape, c.shape, sizeof(int64_t) * c.ndim) != 0 || field_bytes(*fi) != c.item_bytes)
           return fail(BT_E_SCHEMA, "field '%s' changed type or shape", c.key);
         if (!by_ref) {
+          if (fi->payload_off >= kExternalBase) {  // landed by the streaming receiver already
+            const uint64_t e = fi->payload_off - kExternalBase;
+            if (e >= g_ext_cols.size() || g_ext_cols[e] != (int)ci)
+              return fail(BT_E_SCHEMA, "field '%s': streamed payload went to another column", c.key);
+            break;
+          }
           copy_or_defer(dst, msg + fi->payload_off, c.item_bytes, tasks);
           break;
         }

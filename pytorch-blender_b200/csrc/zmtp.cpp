@@ -1,0 +1,492 @@
+// Direct receiver: a minimal ZMTP 3.x PULL endpoint that lands payloads straight from the kernel
+// socket in the pinned staging slot.
+//
+// The reference receives through libzmq (`socket.recv()` at pkg_pytorch/blendtorch/btt/dataset.py:101,105):
+// kernel socket buffer -> libzmq message buffer -> Python bytes -> ndarray.  rx.cpp already removes the
+// Python part; this file also removes libzmq's intermediate buffer for the one thing that matters,
+// the frame payload: the message is scanned *while it arrives* (scan.cpp, streaming mode), and as
+// soon as the scanner stands on the raw data of an array that matches a schema column, the rest of
+// that payload is recv()'d directly into its final position in the slot.  One CPU copy per payload
+// byte on the consumer side (kernel -> pinned) instead of two.
+//
+// Wire compatibility: the peers are unmodified ZMQ PUSH sockets (btb/publisher.py:21-27: PUSH, bind).
+// Implemented: ZMTP 3.0/3.1 greeting, NULL security handshake (READY with Socket-Type=PULL),
+// single-part messages, commands are skipped, reconnect with back-off, fair round-robin over peers,
+// tcp:// and ipc:// endpoints.  Anything else (multipart messages, other mechanisms) is reported and
+// the caller falls back to the libzmq receiver (rx.cpp).
+#include <arpa/inet.h>
+#include <fcntl.h>
+#include <netdb.h>
+#include <netinet/in.h>
+#include <netinet/tcp.h>
+#include <poll.h>
+#include <sys/socket.h>
+#include <sys/un.h>
+#include <time.h>
+#include <unistd.h>
+
+#include <cerrno>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "common.h"
+
+namespace bt {
+// ring.cu: place pre-scanned fields of one message into a ring slot (handles shared-memory refs)
+int ring_place(bt_ring* r, int slot, const bt_schema* s, int item, const uint8_t* msg, const std::vector<bt_field>& f);
+uint8_t* ring_slot_base(bt_ring* r, int slot);
+}  // namespace bt
+
+namespace {
+
+uint64_t now_ms() {
+  struct timespec t;
+  clock_gettime(CLOCK_MONOTONIC, &t);
+  return (uint64_t)t.tv_sec * 1000ull + (uint64_t)t.tv_nsec / 1000000ull;
+}
+
+struct Peer {
+  std::string address;
+  int family = AF_INET;
+  sockaddr_storage addr;
+  socklen_t addrlen = 0;
+  int fd = -1;
+  enum State { IDLE, CONNECTING, READY } state = IDLE;
+  uint64_t retry_at = 0;
+  uint32_t backoff_ms = 20;
+};
+
+struct External {
+  uint64_t compact_pos;
+  uint64_t len;
+  const uint8_t* where;
+};
+
+constexpr int kIoTimeoutMs = 10000;  // a message that started arriving must complete within this
+
+void close_peer(Peer& p) {
+  if (p.fd >= 0) close(p.fd);
+  p.fd = -1;
+  p.state = Peer::IDLE;
+  p.retry_at = now_ms() + p.backoff_ms;
+  if (p.backoff_ms < 500) p.backoff_ms *= 2;
+}
+
+// Blocking-with-deadline I/O on a non-blocking fd.
+int read_exact(int fd, uint8_t* dst, uint64_t n, int timeout_ms) {
+  const uint64_t deadline = now_ms() + (uint64_t)timeout_ms;
+  while (n) {
+    ssize_t k = recv(fd, dst, n > (1u << 30) ? (1u << 30) : (size_t)n, 0);
+    if (k > 0) { dst += k; n -= (uint64_t)k; continue; }
+    if (k == 0) return bt::fail(BT_E_IO, "peer closed the connection");
+    if (errno == EINTR) continue;
+    if (errno != EAGAIN && errno != EWOULDBLOCK) return bt::fail(BT_E_IO, "recv: %s", strerror(errno));
+    const uint64_t now = now_ms();
+    if (now >= deadline) return bt::fail(BT_E_IO, "peer stalled in the middle of a message");
+    pollfd pf = {fd, POLLIN, 0};
+    poll(&pf, 1, (int)(deadline - now));
+  }
+  return BT_OK;
+}
+
+int write_all(int fd, const uint8_t* src, size_t n, int timeout_ms) {
+  const uint64_t deadline = now_ms() + (uint64_t)timeout_ms;
+  while (n) {
+    ssize_t k = send(fd, src, n, MSG_NOSIGNAL);
+    if (k > 0) { src += k; n -= (size_t)k; continue; }
+    if (k < 0 && errno == EINTR) continue;
+    if (k < 0 && errno != EAGAIN && errno != EWOULDBLOCK) return bt::fail(BT_E_IO, "send: %s", strerror(errno));
+    const uint64_t now = now_ms();
+    if (now >= deadline) return bt::fail(BT_E_IO, "peer does not accept the handshake");
+    pollfd pf = {fd, POLLOUT, 0};
+    poll(&pf, 1, (int)(deadline - now));
+  }
+  return BT_OK;
+}
+
+int parse_address(const std::string& a, Peer& p) {
+  memset(&p.addr, 0, sizeof p.addr);
+  if (a.rfind("tcp://", 0) == 0) {
+    const std::string rest = a.substr(6);
+    const size_t colon = rest.rfind(':');
+    if (colon == std::string::npos) return bt::fail(BT_E_INVALID, "address %s has no port", a.c_str());
+    std::string host = rest.substr(0, colon), port = rest.substr(colon + 1);
+    if (!host.empty() && host.front() == '[' && host.back() == ']') host = host.substr(1, host.size() - 2);
+    if (host == "localhost") host = "127.0.0.1";
+    addrinfo hints;
+    memset(&hints, 0, sizeof hints);
+    hints.ai_family = AF_UNSPEC;
+    hints.ai_socktype = SOCK_STREAM;
+    addrinfo* res = nullptr;
+    if (getaddrinfo(host.c_str(), port.c_str(), &hints, &res) != 0 || !res)
+      return bt::fail(BT_E_INVALID, "cannot resolve %s", a.c_str());
+    memcpy(&p.addr, res->ai_addr, res->ai_addrlen);
+    p.addrlen = res->ai_addrlen;
+    p.family = res->ai_family;
+    freeaddrinfo(res);
+    return BT_OK;
+  }
+  if (a.rfind("ipc://", 0) == 0) {
+    const std::string path = a.substr(6);
+    sockaddr_un* un = reinterpret_cast<sockaddr_un*>(&p.addr);
+    if (path.empty() || path.size() >= sizeof un->sun_path) return bt::fail(BT_E_INVALID, "bad ipc path in %s", a.c_str());
+    un->sun_family = AF_UNIX;
+    memcpy(un->sun_path, path.c_str(), path.size());
+    p.addrlen = (socklen_t)(offsetof(sockaddr_un, sun_path) + path.size());
+    if (path[0] == '@') un->sun_path[0] = '\0';  // abstract namespace, as libzmq spells it
+    else p.addrlen += 1;
+    p.family = AF_UNIX;
+    return BT_OK;
+  }
+  return bt::fail(BT_E_UNSUPPORTED, "the direct receiver speaks tcp:// and ipc:// only (%s)", a.c_str());
+}
+
+// ZMTP 3.0 greeting + NULL handshake, synchronously (the peer is a live libzmq engine).
+int handshake(int fd) {
+  uint8_t g[64];
+  memset(g, 0, sizeof g);
+  g[0] = 0xFF; g[8] = 0x01; g[9] = 0x7F;   // signature
+  g[10] = 3; g[11] = 0;                      // version 3.0
+  memcpy(g + 12, "NULL", 4);                 // mechanism, zero padded to 20 bytes; as-server = 0; filler
+  int rc = write_all(fd, g, sizeof g, 2000);
+  if (rc != BT_OK) return rc;
+  uint8_t peer[64];
+  rc = read_exact(fd, peer, sizeof peer, 2000);
+  if (rc != BT_OK) return rc;
+  if (peer[0] != 0xFF || peer[9] != 0x7F || peer[10] < 3)
+    return bt::fail(BT_E_UNSUPPORTED, "peer does not speak ZMTP 3");
+  if (memcmp(peer + 12, "NULL\0", 5) != 0)
+    return bt::fail(BT_E_UNSUPPORTED, "peer uses a security mechanism other than NULL");
+  static const uint8_t ready[] = {0x04, 26, 5, 'R', 'E', 'A', 'D', 'Y', 11, 'S', 'o', 'c', 'k', 'e', 't', '-', 'T', 'y', 'p', 'e',
+                                  0, 0, 0, 4, 'P', 'U', 'L', 'L'};
+  rc = write_all(fd, ready, sizeof ready, 2000);
+  if (rc != BT_OK) return rc;
+  // the peer's READY (a command frame)
+  uint8_t h[9];
+  rc = read_exact(fd, h, 2, 2000);
+  if (rc != BT_OK) return rc;
+  if (!(h[0] & 0x04)) return bt::fail(BT_E_UNSUPPORTED, "expected a ZMTP command, got flags 0x%02x", h[0]);
+  uint64_t size = h[1];
+  if (h[0] & 0x02) {
+    rc = read_exact(fd, h + 2, 7, 2000);
+    if (rc != BT_OK) return rc;
+    size = 0;
+    for (int i = 1; i < 9; ++i) size = (size << 8) | h[i];
+  }
+  if (size < 6 || size > 4096) return bt::fail(BT_E_UNSUPPORTED, "unexpected handshake command size");
+  std::vector<uint8_t> body(size);
+  rc = read_exact(fd, body.data(), size, 2000);
+  if (rc != BT_OK) return rc;
+  if (body[0] != 5 || memcmp(&body[1], "READY", 5) != 0) return bt::fail(BT_E_UNSUPPORTED, "peer refused the connection");
+  return BT_OK;
+}
+
+}  // namespace
+
+struct bt_pull {
+  std::vector<Peer> peers;
+  size_t rr = 0;
+  std::vector<uint8_t> cb;    // message in progress, large payloads cut out
+  std::vector<uint8_t> held;  // a complete message kept for the caller
+  bool has_held = false;
+  std::vector<External> ext;
+  std::vector<pollfd> pfds;
+  uint64_t messages = 0, bytes = 0;
+};
+
+namespace {
+
+void start_connect(Peer& p) {
+  p.fd = socket(p.family, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
+  if (p.fd < 0) { p.retry_at = now_ms() + 200; return; }
+  int big = 4 << 20;
+  setsockopt(p.fd, SOL_SOCKET, SO_RCVBUF, &big, sizeof big);
+  int rc = connect(p.fd, reinterpret_cast<sockaddr*>(&p.addr), p.addrlen);
+  if (rc == 0 || errno == EINPROGRESS) {
+    p.state = Peer::CONNECTING;
+  } else {
+    close_peer(p);
+  }
+}
+
+void finish_connect(Peer& p) {
+  int err = 0;
+  socklen_t len = sizeof err;
+  if (getsockopt(p.fd, SOL_SOCKET, SO_ERROR, &err, &len) != 0 || err != 0 || handshake(p.fd) != BT_OK) {
+    close_peer(p);
+    return;
+  }
+  p.state = Peer::READY;
+  p.backoff_ms = 20;
+}
+
+// Drive the connections; return the index of a READY peer with bytes to read, or -1 after timeout_ms.
+int wait_readable(bt_pull* q, int timeout_ms) {
+  const uint64_t deadline = now_ms() + (uint64_t)(timeout_ms < 0 ? 0 : timeout_ms);
+  while (true) {
+    const uint64_t now = now_ms();
+    q->pfds.clear();
+    uint64_t next_retry = ~0ull;
+    for (Peer& p : q->peers) {
+      if (p.state == Peer::IDLE && now >= p.retry_at) start_connect(p);
+      pollfd pf = {-1, 0, 0};
+      if (p.state == Peer::CONNECTING) pf = {p.fd, POLLOUT, 0};
+      else if (p.state == Peer::READY) pf = {p.fd, POLLIN, 0};
+      else if (p.retry_at < next_retry) next_retry = p.retry_at;
+      q->pfds.push_back(pf);
+    }
+    int wait = now >= deadline ? 0 : (int)(deadline - now);
+    if (next_retry != ~0ull) {
+      const int until = next_retry > now ? (int)(next_retry - now) : 0;
+      if (until < wait) wait = until;
+    }
+    poll(q->pfds.data(), q->pfds.size(), wait);
+    const size_t n = q->peers.size();
+    for (size_t k = 0; k < n; ++k) {
+      Peer& p = q->peers[k];
+      if (p.state == Peer::CONNECTING && (q->pfds[k].revents & (POLLOUT | POLLERR | POLLHUP))) finish_connect(p);
+    }
+    for (size_t k = 0; k < n; ++k) {
+      const size_t i = (q->rr + k) % n;
+      Peer& p = q->peers[i];
+      if (p.state != Peer::READY) continue;
+      if (q->pfds[i].revents & POLLIN) {
+        q->rr = (i + 1) % n;
+        return (int)i;
+      }
+      if (q->pfds[i].revents & (POLLERR | POLLHUP | POLLNVAL)) close_peer(p);
+    }
+    if (now_ms() >= deadline) return -1;
+  }
+}
+
+// Read one frame header.  *is_msg = 0 for a command (skipped), 1 for a message of `*size` bytes.
+int read_frame_header(Peer& p, int* is_msg, uint64_t* size) {
+  uint8_t h[9];
+  int rc = read_exact(p.fd, h, 2, kIoTimeoutMs);
+  if (rc != BT_OK) return rc;
+  uint64_t sz = h[1];
+  if (h[0] & 0x02) {
+    rc = read_exact(p.fd, h + 2, 7, kIoTimeoutMs);
+    if (rc != BT_OK) return rc;
+    sz = 0;
+    for (int i = 1; i < 9; ++i) sz = (sz << 8) | h[i];
+  }
+  if (h[0] & 0x04) {  // command (PING, ERROR, ...): skip
+    std::vector<uint8_t> skip(sz > 65536 ? 65536 : sz);
+    uint64_t left = sz;
+    while (left) {
+      const uint64_t k = left < skip.size() ? left : skip.size();
+      rc = read_exact(p.fd, skip.data(), k, kIoTimeoutMs);
+      if (rc != BT_OK) return rc;
+      left -= k;
+    }
+    *is_msg = 0;
+    return BT_OK;
+  }
+  if (h[0] & 0x01) return bt::fail(BT_E_IO, "multipart messages are not part of the blendtorch wire (publisher.py:43)");
+  if (sz > (1ull << 40)) return bt::fail(BT_E_IO, "implausible message size");
+  *is_msg = 1;
+  *size = sz;
+  return BT_OK;
+}
+
+// Whole message into q->held.
+int read_whole(bt_pull* q, Peer& p, uint64_t size) {
+  q->held.resize(size);
+  int rc = read_exact(p.fd, q->held.data(), size, kIoTimeoutMs);
+  if (rc != BT_OK) return rc;
+  q->has_held = true;
+  return BT_OK;
+}
+
+// Rebuild the original bytes of a partly streamed message (compact buffer + landed payloads) and
+// read the rest of it, so that the caller can hand it to pickle.loads.
+int rebuild_into_held(bt_pull* q, Peer& p, uint64_t msg_size, uint64_t consumed) {
+  std::vector<uint8_t>& out = q->held;
+  out.clear();
+  out.reserve(msg_size);
+  uint64_t from = 0;
+  for (const External& e : q->ext) {
+    out.insert(out.end(), q->cb.begin() + from, q->cb.begin() + e.compact_pos);
+    out.insert(out.end(), e.where, e.where + e.len);
+    from = e.compact_pos;
+  }
+  out.insert(out.end(), q->cb.begin() + from, q->cb.end());
+  const uint64_t have = out.size();
+  if (have != consumed) return bt::fail(BT_E_IO, "internal: streamed byte count mismatch");
+  out.resize(msg_size);
+  int rc = read_exact(p.fd, out.data() + have, msg_size - have, kIoTimeoutMs);
+  if (rc != BT_OK) return rc;
+  q->has_held = true;
+  return BT_OK;
+}
+
+// Receive one message from `p` and place it as item `item` of the slot, payloads going straight
+// from the socket into the slot.  BT_OK: placed.  BT_E_UNSUPPORTED / BT_E_SCHEMA: the message is in
+// q->held for the caller's pickle.loads path.  BT_E_IO: the connection is unusable.
+int receive_streaming(bt_pull* q, Peer& p, uint64_t msg_size, bt_ring* ring, int slot, const bt_schema* schema, int item) {
+  constexpr uint64_t kChunk = 4096;
+  uint8_t* base = bt::ring_slot_base(ring, slot);
+  q->cb.clear();
+  q->ext.clear();
+  bt::stream_begin();
+  uint64_t consumed = 0;
+  int why = BT_OK;       // != BT_OK: why this message has to go through the caller's decode
+  bool complete = false;
+  while (!complete && why == BT_OK) {
+    const uint64_t want = msg_size - consumed < kChunk ? msg_size - consumed : kChunk;
+    if (want == 0) { why = BT_E_UNSUPPORTED; break; }  // the pickle wants more bytes than the frame has
+    const size_t old = q->cb.size();
+    q->cb.resize(old + want);
+    int rc = read_exact(p.fd, q->cb.data() + old, want, kIoTimeoutMs);
+    if (rc != BT_OK) return rc;
+    consumed += want;
+    // run the scanner over what is buffered; it may stop on several large payloads in a row
+    while (true) {
+      rc = bt::stream_run(q->cb.data(), q->cb.size());
+      if (rc == BT_E_TRUNCATED) break;                 // needs the next chunk
+      if (rc == BT_OK) { complete = true; break; }     // STOP reached
+      if (rc != 1) { why = rc; break; }                // outside the subset
+      const uint64_t len = bt::stream_big_len(), pos = bt::stream_pos();
+      const uint64_t have = q->cb.size() - pos;        // payload bytes that came with the last chunk
+      int col = -1;
+      const int trc = bt::stream_big_target(schema, &col);
+      if (trc != BT_OK || len - have > msg_size - consumed) {
+        // cannot land it: its first bytes stay at the end of the compact buffer, which is where
+        // they belong in the original byte stream, so the rebuild below stays correct
+        why = trc == BT_E_SCHEMA ? BT_E_SCHEMA : BT_E_UNSUPPORTED;
+        break;
+      }
+      const bt_column& c = schema->cols[col];
+      uint8_t* dst = base + c.slot_off + c.item_bytes * (uint64_t)item;
+      memcpy(dst, q->cb.data() + pos, have);
+      q->cb.resize(pos);
+      rc = read_exact(p.fd, dst + have, len - have, kIoTimeoutMs);
+      if (rc != BT_OK) return rc;
+      consumed += len - have;
+      q->ext.push_back(External{pos, len, dst});
+    }
+  }
+  if (why == BT_OK) {
+    if (consumed < msg_size) {  // bytes after the pickle's STOP: not ours to interpret
+      std::vector<uint8_t> tail(msg_size - consumed);
+      int rc = read_exact(p.fd, tail.data(), tail.size(), kIoTimeoutMs);
+      if (rc != BT_OK) return rc;
+      q->cb.insert(q->cb.end(), tail.begin(), tail.end());
+      consumed = msg_size;
+    }
+    std::vector<bt_field>& f = bt::tls_fields();
+    int rc = bt::stream_fields(q->cb.data(), f);
+    if (rc == BT_OK) rc = bt::ring_place(ring, slot, schema, item, q->cb.data(), f);
+    if (rc == BT_OK) return BT_OK;
+    why = rc == BT_E_SCHEMA ? BT_E_SCHEMA : BT_E_UNSUPPORTED;
+  }
+  const std::string reason = bt::last_error_ref();
+  int rc = rebuild_into_held(q, p, msg_size, consumed);
+  if (rc != BT_OK) return rc;
+  bt::last_error_ref() = reason;
+  return why;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bt_pull_create(bt_pull** out) {
+  if (!out) return bt::fail(BT_E_INVALID, "bt_pull_create: null argument");
+  bt_pull* q = new (std::nothrow) bt_pull();
+  if (!q) return bt::fail(BT_E_NOMEM, "out of memory");
+  *out = q;
+  return BT_OK;
+}
+
+int bt_pull_connect(bt_pull* q, const char* address) {
+  if (!q || !address) return bt::fail(BT_E_INVALID, "bt_pull_connect: null argument");
+  Peer p;
+  p.address = address;
+  int rc = parse_address(p.address, p);
+  if (rc != BT_OK) return rc;
+  q->peers.push_back(p);
+  return BT_OK;
+}
+
+int bt_pull_destroy(bt_pull* q) {
+  if (!q) return BT_OK;
+  for (Peer& p : q->peers)
+    if (p.fd >= 0) close(p.fd);
+  delete q;
+  return BT_OK;
+}
+
+int bt_pull_recv(bt_pull* q, int timeout_ms) {
+  if (!q) return bt::fail(BT_E_INVALID, "null receiver");
+  if (q->has_held) return BT_OK;
+  const uint64_t deadline = now_ms() + (uint64_t)(timeout_ms < 0 ? 0 : timeout_ms);
+  while (true) {
+    const uint64_t now = now_ms();
+    const int i = wait_readable(q, now >= deadline ? 0 : (int)(deadline - now));
+    if (i < 0) return BT_E_TIMEOUT;
+    Peer& p = q->peers[i];
+    int is_msg = 0;
+    uint64_t size = 0;
+    int rc = read_frame_header(p, &is_msg, &size);
+    if (rc == BT_OK && is_msg) rc = read_whole(q, p, size);
+    if (rc != BT_OK) { close_peer(p); continue; }
+    if (is_msg) return BT_OK;
+  }
+}
+
+int bt_pull_pending(bt_pull* q, const uint8_t** data, uint64_t* len) {
+  if (!q || !data || !len) return bt::fail(BT_E_INVALID, "bt_pull_pending: bad arguments");
+  if (!q->has_held) {
+    *data = nullptr;
+    *len = 0;
+    return bt::fail(BT_E_INVALID, "no message is held");
+  }
+  *data = q->held.data();
+  *len = q->held.size();
+  return BT_OK;
+}
+
+int bt_pull_drop(bt_pull* q) {
+  if (!q) return bt::fail(BT_E_INVALID, "null receiver");
+  q->has_held = false;
+  return BT_OK;
+}
+
+int bt_pull_fill(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, int first_item, int max_items,
+                 int slice_ms, int* n_done) {
+  if (!q || !ring || !schema || !n_done || first_item < 0 || max_items < 0 || first_item + max_items > schema->batch)
+    return bt::fail(BT_E_INVALID, "bt_pull_fill: bad arguments");
+  *n_done = 0;
+  while (*n_done < max_items) {
+    if (q->has_held) {  // the first message of the stream, received before the schema existed
+      int rc = bt_ring_ingest(ring, slot, schema, first_item + *n_done, q->held.data(), q->held.size());
+      if (rc != BT_OK) return rc;
+      q->has_held = false;
+      ++*n_done;
+      continue;
+    }
+    const int i = wait_readable(q, slice_ms);
+    if (i < 0) return BT_E_TIMEOUT;
+    Peer& p = q->peers[i];
+    int is_msg = 0;
+    uint64_t size = 0;
+    int rc = read_frame_header(p, &is_msg, &size);
+    if (rc != BT_OK) { close_peer(p); continue; }
+    if (!is_msg) continue;
+    rc = receive_streaming(q, p, size, ring, slot, schema, first_item + *n_done);
+    if (rc == BT_E_UNSUPPORTED || rc == BT_E_SCHEMA) return rc;  // message is held for the caller
+    if (rc != BT_OK) { close_peer(p); continue; }
+    q->messages++;
+    q->bytes += size;
+    ++*n_done;
+    bt_ring_reap(ring);
+  }
+  return BT_OK;
+}
+
+}  // extern "C"

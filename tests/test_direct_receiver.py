@@ -1,0 +1,165 @@
+"""The direct ZMTP receiver (bt_pull_*) against unmodified pyzmq PUSH sockets: handshake, framing,
+streaming placement of payloads (large ones never enter the message buffer), fallback to the caller's
+pickle.loads for messages outside the subset, several publishers, late publishers, ipc://."""
+import os
+import pickle
+import threading
+import time
+
+import numpy as np
+import pytest
+import zmq
+from torch.utils.data import default_collate
+
+from blendtorch import btt
+from blendtorch.btt import native as N
+from blendtorch.btt.rx import DirectReceiver
+from blendtorch.btt.staging import Ring, Schema
+
+
+def _msgs(n, shape=(120, 160, 4), seed=0, extra=False):
+    rng = np.random.default_rng(seed)
+    out = []
+    for i in range(n):
+        m = {"btid": seed, "image": rng.integers(0, 256, shape, dtype=np.uint8), "frameid": i,
+             "bbox": rng.random((8, 4)).astype(np.float32)}
+        if extra:
+            m["depth"] = rng.random(shape[:2], dtype=np.float32)      # a second large payload after the first
+            m["score"] = float(i) / 3
+        out.append(m)
+    return out
+
+
+def _publisher(addr, blobs, delay=0.0):
+    def run():
+        time.sleep(delay)
+        ctx = zmq.Context()
+        s = ctx.socket(zmq.PUSH)
+        s.setsockopt(zmq.SNDHWM, 10)
+        s.setsockopt(zmq.LINGER, 5000)
+        s.setsockopt(zmq.IMMEDIATE, 1)
+        s.bind(addr)
+        for b in blobs:
+            s.send(b)
+        s.close()
+        ctx.term()
+    t = threading.Thread(target=run)
+    t.start()
+    return t
+
+
+def _free_tcp():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return "tcp://127.0.0.1:%d" % p
+
+
+def _drain(rx, sch, total, B, on_odd=None):
+    ring = Ring(sch.slot_bytes, depth=2, device=None)
+    batches, placed, waited = [], 0, 0
+    while placed < total:
+        slot, filled = ring.acquire(), 0
+        want = min(B, total - placed)
+        while filled < want:
+            rc, n = rx.fill(ring, slot, sch, filled, want - filled, 200)
+            filled += n
+            if rc == N.BT_OK:
+                break
+            if rc == N.BT_E_TIMEOUT:
+                waited += 200
+                assert waited < 20000, "publishers went silent"
+                continue
+            obj = pickle.loads(rx.pending())       # outside the subset: the reference's own decode
+            if on_odd:
+                obj = on_odd(obj)
+            sch.ingest_object(ring.view(slot), filled, obj)
+            rx.drop()
+            filled += 1
+        v = ring.view(slot)
+        batches.append({c.key: v[c.slot_off:c.slot_off + filled * c.item_bytes].view(c.dtype).reshape((filled,) + c.shape).copy()
+                        for c in sch.columns})
+        placed += filled
+    ring.close()
+    return batches
+
+
+@pytest.mark.parametrize("protocol", [3, 4, 5])
+@pytest.mark.parametrize("extra", [False, True])
+def test_streams_from_an_unmodified_push_socket(protocol, extra):
+    msgs = _msgs(7, extra=extra)
+    addr = _free_tcp()
+    t = _publisher(addr, [pickle.dumps(m, protocol=protocol) for m in msgs])
+    rx = DirectReceiver([addr])
+    deadline = time.time() + 20
+    while not rx.recv(200):
+        assert time.time() < deadline
+    sch = Schema.from_message(rx.pending(), 3)
+    got = _drain(rx, sch, 7, 3)
+    t.join()
+    rx.close()
+    exp = default_collate(msgs)
+    assert [len(b["frameid"]) for b in got] == [3, 3, 1]
+    for key in exp:
+        cat = np.concatenate([b[key] for b in got])
+        assert cat.dtype == exp[key].numpy().dtype, key
+        np.testing.assert_array_equal(cat, exp[key].numpy())
+
+
+def test_odd_messages_small_messages_and_two_publishers():
+    a1, a2 = _free_tcp(), "ipc:///tmp/bt_direct_test_%d" % os.getpid()
+    m1, m2 = _msgs(6, seed=1), _msgs(5, seed=2)
+    odd = dict(m1[3], image=np.zeros((60, 80, 4), np.uint8))          # wrong shape: rejected while streaming
+    blobs1 = [pickle.dumps(odd if i == 3 else m, protocol=3) for i, m in enumerate(m1)]
+    t1 = _publisher(a1, blobs1)
+    t2 = _publisher(a2, [pickle.dumps(m, protocol=4) for m in m2], delay=0.5)     # comes up late: retried
+    rx = DirectReceiver([a1, a2])
+    deadline = time.time() + 20
+    while not rx.recv(200):
+        assert time.time() < deadline
+    sch = Schema.from_message(rx.pending(), 4)
+    seen_odd = []
+
+    def fix(obj):
+        seen_odd.append(obj["image"].shape)
+        obj["image"] = m1[3]["image"]
+        return obj
+
+    got = _drain(rx, sch, 11, 4, on_odd=fix)
+    t1.join()
+    t2.join()
+    rx.close()
+    assert seen_odd == [(60, 80, 4)]
+    rows = {}
+    for b in got:
+        for i in range(len(b["frameid"])):
+            rows[(int(b["btid"][i]), int(b["frameid"][i]))] = (b["image"][i], b["bbox"][i])
+    assert len(rows) == 11                                   # every message exactly once
+    for seed, ms in ((1, m1), (2, m2)):
+        for m in ms:
+            img, bb = rows[(seed, m["frameid"])]
+            np.testing.assert_array_equal(img, m["image"])
+            np.testing.assert_array_equal(bb, m["bbox"])
+    # tiny messages (no payload worth streaming) and the reference's own test message
+    addr = _free_tcp()
+    small = [{"btid": 0, "frameid": i, "img": np.zeros((64, 64), np.uint8)} for i in range(5)]
+    t = _publisher(addr, [pickle.dumps(m, protocol=3) for m in small])
+    rx = DirectReceiver([addr])
+    while not rx.recv(200):
+        pass
+    sch = Schema.from_message(rx.pending(), 5)
+    got = _drain(rx, sch, 5, 5)
+    t.join()
+    rx.close()
+    np.testing.assert_array_equal(got[0]["frameid"], np.arange(5))
+    assert got[0]["img"].shape == (5, 64, 64)
+
+
+def test_rejects_what_it_does_not_speak():
+    with pytest.raises(N.NativeError):
+        DirectReceiver(["inproc://x"])
+    rx = DirectReceiver([_free_tcp()])        # nobody there: time-out, not an error
+    assert rx.recv(150) is False
+    rx.close()

@@ -255,3 +255,37 @@ def test_replay_with_several_producers_keeps_order(golden_dir, producers):
     assert [len(b["frameid"]) for b in dl] == [4, 4]
     assert [b["frameid"].tolist() for b in dl] == [[0, 1, 2, 3], [4, 5, 0, 1]]
     dl.close()
+
+
+def test_stream_through_the_direct_receiver():
+    """transport='direct': the library's own ZMTP endpoint instead of pyzmq's socket; same batches."""
+    H, W, pubs, per_pub = 48, 64, 2, 8
+    addrs = ["tcp://127.0.0.1:%d" % _free_port() for _ in range(pubs)]
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=_publisher, args=(a, i, per_pub, per_pub, H, W, 2, 3 + i), daemon=True)
+             for i, a in enumerate(addrs)]
+    for p in procs:
+        p.start()
+    try:
+        ds = btt.RemoteIterableDataset(addrs, max_items=per_pub * pubs, timeoutms=20000)
+        dl = btt.DeviceLoader(ds, batch_size=4, device=DEV, keep_raw=True, transport="direct",
+                              preprocess=btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5))
+        got = {}
+        for b in dl:
+            raw = b["image_raw"].cpu().numpy()
+            np.testing.assert_array_equal(b["image"].cpu().numpy(),
+                                          opre.preprocess_batch(list(raw), flip=True, gamma=2.2, mean=127.5, std=127.5))
+            for i in range(len(raw)):
+                key = (int(b["btid"][i]), int(b["frameid"][i]))
+                assert key not in got
+                got[key] = (raw[i], b["bbox"][i].cpu().numpy())
+        assert len(got) == per_pub * pubs and dl.stats["compat_items"] == 0
+        for btid in range(pubs):
+            rng = S.rng_for(2, btid)
+            for i in range(per_pub):
+                m = S.message(rng, 2, btid, i, H, W)
+                np.testing.assert_array_equal(got[(btid, i)][0], m["image"])
+                np.testing.assert_array_equal(got[(btid, i)][1], m["bbox"])
+    finally:
+        for p in procs:
+            p.join(timeout=10)

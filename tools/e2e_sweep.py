@@ -28,8 +28,9 @@ def main():
         transport, recv, io = combo[:3]
         shm_slots = combo[3] if len(combo) > 3 else 0
         bench.PUBLISHERS = combo[4] if len(combo) > 4 else 5
-        images, sec, h2d, d2h = bench.e2e_leg(torch, btt, dev, 600, 10, _S(), transport, recv, io, shm_slots)
-        r = {"transport": transport, "receivers": recv, "io_threads": io, "shm_slots": shm_slots,
+        rxmode = combo[5] if len(combo) > 5 else "auto"
+        images, sec, h2d, d2h = bench.e2e_leg(torch, btt, dev, 600, 10, _S(), transport, recv, io, shm_slots, rxmode)
+        r = {"transport": transport, "rx": rxmode, "receivers": recv, "io_threads": io, "shm_slots": shm_slots,
              "publishers": bench.PUBLISHERS, "images_per_s": images / sec,
              "GBps": images / sec * 1228800 / 1e9}
         print(json.dumps(r), flush=True)
