@@ -19,6 +19,19 @@ for p in (str(ROOT), str(PKG)):
 GOLDEN = Path(__file__).resolve().parent / "golden"
 
 
+def _ensure_native_library():
+    """The C-ABI library is built in-tree and is not in git history: build it (nvcc, a few seconds; a
+    no-op when it is up to date) so that a fresh checkout can run the suite."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bt_build_native", PKG / "build_native.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.build()
+
+
+_ensure_native_library()
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 
