@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(kThreads) k1_planar(K1Args a, PlanarGeom g) {
 // thread's result is exactly one 16-byte store and a warp writes 512 contiguous bytes per store
 // instruction (fp32: 4 bytes in -> float4 out; bf16: 8 -> 16; u8: 16 -> 16).  Needs Cout == C.
 // IDENT (u8 without gamma) skips the table: the kernel is then a flipping copy.
-template <typename T, int UNROLL, bool STATS, bool IDENT>
+template <typename T, int UNROLL, bool STATS, bool IDENT, int CFIX>
 __global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a, PlanarGeom g) {
   constexpr int IB = 16 / (int)sizeof(T);
   constexpr int LW = IB;  // one load per unit
@@ -342,11 +342,13 @@ __global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a, PlanarGeom 
     for (int j = 0; j < UNROLL; ++j) {
       if (!live[j]) continue;
       T vals[IB];
-      uint32_t c = phase[j];
+      uint32_t c = CFIX ? 0u : phase[j];   // RGBA units start on a pixel boundary (IB is a multiple of 4)
 #pragma unroll
       for (int k = 0; k < IB; ++k) {
+        if (CFIX == 4) c = k & 3;
         const uint32_t v = byte_of(in[j], k);
-        if constexpr (IDENT) vals[k] = OutT<T>::make((float)v, (uint8_t)v);
+        // uint8 output has no normalisation and gamma leaves alpha alone: channel 3 passes through
+        if (IDENT || (sizeof(T) == 1 && CFIX == 4 && (k & 3) == 3)) vals[k] = OutT<T>::make((float)v, (uint8_t)v);
         else vals[k] = lut[c * 256 + v];
         if (STATS) {
           float f = OutT<T>::as_float(vals[k]);
@@ -354,7 +356,7 @@ __global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a, PlanarGeom 
           for (int cc = 0; cc < kMaxC; ++cc)
             if (cc == (int)c) { acc.s[cc] += f; acc.q[cc] += (double)f * f; }
         }
-        c = (c + 1 == C) ? 0 : c + 1;
+        if (CFIX == 0) c = (c + 1 == C) ? 0 : c + 1;
       }
       st_stream<T, IB>(dst + out_off[j], vals);
     }
@@ -509,7 +511,15 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
   if (can_vec && p->chw && a.C == 4) {
     // widest unit whose stores are 16 bytes and that divides the row
     if (sizeof(T) == 1 && a.W % 16 == 0) LAUNCH_PLANAR(4, 16, 2);
-    if (sizeof(T) == 2 && a.W % 8 == 0) LAUNCH_PLANAR(4, 8, 2);
+    if (sizeof(T) == 2 && a.W % 8 == 0) {
+      if (!STATS && tune_unroll == 4) LAUNCH_PLANAR(4, 8, 4);
+      if (!STATS && tune_unroll == 1) LAUNCH_PLANAR(4, 8, 1);
+      if (!STATS && tune_unroll == 44) LAUNCH_PLANAR(4, 4, 4);
+      // large batches: more bytes in flight per thread (0.905 vs 0.871 of peak at 64 x 1024^2);
+      // small ones keep the shorter critical path
+      if (!STATS && tune_unroll == 0 && rows * (a.W / 8) >= (1u << 20)) LAUNCH_PLANAR(4, 8, 4);
+      LAUNCH_PLANAR(4, 8, 2);
+    }
     if (a.W % 4 == 0) {
       if (!STATS && sizeof(T) == 4) {
         if (tune_unroll == 1) LAUNCH_PLANAR(4, 4, 1);
@@ -539,9 +549,13 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
         geo.total_units = (uint32_t)total;
         int g = grid_of(total, 4);
         if (sizeof(T) == 1 && !a.use_gamma)
-          k1_interleaved<T, 4, STATS, true><<<g, kThreads, 0, st>>>(a, geo);
+          k1_interleaved<T, 4, STATS, true, 0><<<g, kThreads, 0, st>>>(a, geo);
+        else if (a.C == 4)
+          k1_interleaved<T, 4, STATS, false, 4><<<g, kThreads, 0, st>>>(a, geo);
+        else if (a.C == 1)
+          k1_interleaved<T, 4, STATS, false, 1><<<g, kThreads, 0, st>>>(a, geo);
         else
-          k1_interleaved<T, 4, STATS, false><<<g, kThreads, 0, st>>>(a, geo);
+          k1_interleaved<T, 4, STATS, false, 0><<<g, kThreads, 0, st>>>(a, geo);
         g_last_variant = 2;
         return g;
       }

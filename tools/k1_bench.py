@@ -89,7 +89,17 @@ def main():
         dict(shape=C3, dtype=torch.float32), dict(shape=C5, dtype=torch.float32),
         dict(shape=(8, 480, 640, 3), dtype=torch.float32), dict(shape=(8, 481, 641, 4), dtype=torch.float32),
     ]
-    if len(sys.argv) > 1 and sys.argv[1] == "pdl":
+    if len(sys.argv) > 1 and sys.argv[1] == "bf16":
+        cases = [dict(shape=sh, dtype=torch.bfloat16, tune=t, streams=st) for sh in (C4, C2) for t in (0, 4, 1, 44)
+                 for st in ((1, 4) if sh == C2 else (1,))]
+        cases += [dict(shape=(64, 1024, 1024, 1), dtype=torch.float32)]
+    elif len(sys.argv) > 1 and sys.argv[1] == "extra":
+        cases = [dict(shape=C4, dtype=torch.uint8, layout="NHWC"), dict(shape=C4, dtype=torch.uint8, layout="NHWC", gamma=None),
+                 dict(shape=C4, dtype=torch.float32, layout="NHWC"), dict(shape=C4, dtype=torch.bfloat16, layout="NHWC"),
+                 dict(shape=(64, 1024, 1024, 3), dtype=torch.float32), dict(shape=(64, 1024, 1024, 3), dtype=torch.uint8, layout="NHWC"),
+                 dict(shape=(64, 1024, 1024, 1), dtype=torch.float32), dict(shape=C4, dtype=torch.uint8),
+                 dict(shape=C2, dtype=torch.bfloat16, streams=4), dict(shape=C2, dtype=torch.uint8, layout="NHWC", streams=4)]
+    elif len(sys.argv) > 1 and sys.argv[1] == "pdl":
         cases = []
         for shape in (C2, (16, 480, 640, 4), C4):
             for dt in (torch.float32, torch.bfloat16):
