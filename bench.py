@@ -422,6 +422,11 @@ def ours(args):
     e2e_sec = max_over_ranks(e2e_sec)
     images = sum_over_ranks(images)
     e2e_value = images / e2e_sec
+    # same leg with the publishers bound to ipc:// endpoints (the reference's launcher takes any ZMQ proto)
+    barrier()
+    ipc_images, ipc_sec, _, _ = e2e_leg(torch, btt, dev, args.steps, args.warmup, sampler, "ipc", args.receivers)
+    barrier()
+    ipc_value = sum_over_ranks(ipc_images) / max_over_ranks(ipc_sec)
     # same leg over the opt-in shared-memory wire (payload by DMA from the producers' segments)
     barrier()
     shm_images, shm_sec, _, _ = e2e_leg(torch, btt, dev, args.steps, args.warmup, sampler, args.transport,
@@ -452,6 +457,7 @@ def ours(args):
                              "launches replayed from a CUDA graph over %d streams (the pipeline runs one stream per receiver)"
                              % (ROTATE, ROTATE * BATCH * H * W * C * 5 / 1e6, DEVICE_STREAMS),
                        "e2e_transport": args.transport, "e2e_receivers": args.receivers,
+                       "e2e_receiver": "direct ZMTP endpoint (bt_pull_*), unmodified PUSH publishers",
                        "parallelism": "dp%d, publishers sharded per GPU, no collective" % world},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": measured_traffic(), "peak_source": peak_src,
@@ -465,6 +471,9 @@ def ours(args):
             "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "gbs_h2d": e2e_value * h2d_bytes_img / 1e9 / world, "pcie_h2d_measured_gbs": h2d_gbs.value,
                     "frac_of_pcie_h2d": e2e_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value},
+            "e2e_ipc": {"value": ipc_value, "unit": "images/s", "gbs_h2d": ipc_value * h2d_bytes_img / 1e9 / world,
+                        "frac_of_pcie_h2d": ipc_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value,
+                        "note": "as e2e, publishers bound to ipc:// instead of tcp://"},
             "e2e_shm_wire": {"value": shm_value, "unit": "images/s", "gbs_h2d": shm_value * h2d_bytes_img / 1e9 / world,
                              "frac_of_pcie_h2d": shm_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value,
                              "note": "opt-in wire for co-located producers (DataPublisher(shm_slots=%d)): payload goes "
@@ -500,7 +509,7 @@ def main():
         # cores with their N x 5 publisher processes
         n = max(1, int(os.environ.get("WORLD_SIZE", args.gpus)))
         spare = (os.cpu_count() or 1) - PUBLISHERS * n
-        args.receivers = min(4, max(1, spare // (2 * n)))
+        args.receivers = min(8, max(1, spare // n))   # direct receiver: one thread per receiver
     args.shm_receivers = min(args.shm_receivers, args.receivers)
     if args.impl == "reference":
         return reference_arm(args)

@@ -139,12 +139,12 @@ class DeviceLoader:
         batches; the sampler's batch order is preserved.
     ring_depth: pinned slots per receiver.  prefetch: finished batches queued ahead of the consumer.
     ingest_threads: host threads `bt_schema_ingest_many` uses per replay batch.
-    transport: how streams are received.  'zmq' (= 'auto', the default): pyzmq's socket drained by the C
-        loop.  'direct': the library's own ZMTP endpoint (tcp:// and ipc://, no libzmq): payloads go
-        from the kernel socket straight into pinned staging -- one copy less per byte, less CPU per
-        message, but the kernel read is not overlapped by a separate I/O thread, so use more
-        receivers.  Streams with a recording tee or an item_transform always use pyzmq with the
-        per-message Python loop.
+    transport: how streams are received.  'direct' (= 'auto' for tcp:// and ipc:// addresses): the
+        library's own ZMTP endpoint, no libzmq: payloads go from the kernel socket straight into pinned
+        staging -- one copy and one thread per message instead of two of each; give it about twice
+        the receivers you would give pyzmq.  'zmq': pyzmq's socket drained by the C loop (its I/O thread
+        overlaps the kernel read with our copy).  Streams with a recording tee or an item_transform
+        always use pyzmq with the per-message Python loop.
     io_threads: ZMQ I/O threads per receiver; a receiver's connections (one per publisher) are
         spread over them, so socket reads of different publishers proceed in parallel.
     seed: shuffle seed (epoch number is added on every new iteration).
@@ -276,9 +276,9 @@ class DeviceLoader:
         try:
             torch.cuda.set_device(self.device)
             fast = ds.record_path_prefix is None and not ds.has_custom_item()
-            # 'auto' keeps pyzmq's socket: its I/O thread overlaps the kernel read with our copy, which
-            # measured faster per receiver than the direct endpoint on a 16-core host
-            direct = fast and self.transport == "direct" and direct_capable(ds.addresses)
+            # 'auto' prefers the direct endpoint: one thread and one copy per message instead of two of
+            # each; with enough receivers it is the faster path on a busy host
+            direct = fast and self.transport != "zmq" and direct_capable(ds.addresses)
             if self.transport == "direct" and not direct:
                 raise ValueError("transport='direct' needs tcp:// or ipc:// addresses, no recording tee and no item_transform")
             if not direct:
