@@ -186,3 +186,28 @@ def test_full_size_properties(name, shape):
     bf = btt.preprocess_images(src, btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5, dtype=torch.bfloat16))
     exp = _lut_expected(src, lut, True, True).to(torch.bfloat16)
     assert torch.equal(bf, exp)
+
+
+def test_bulk_async_variant_matches_the_register_variant():
+    """variant='bulk' (cp.async.bulk + mbarrier ring staging the input in shared memory) is the measured
+    A/B partner of the register-vectorised kernel: identical bits, including ragged last segments
+    (W*4 not a multiple of the 4 KiB segment), flips, alpha dropped, every output type."""
+    from blendtorch.btt import native as N
+    rng = np.random.default_rng(21)
+    for shape in ((3, 9, 1028, 4), (2, 5, 640, 4), (1, 3, 4, 4), (2, 17, 2052, 4), (40, 33, 64, 4)):
+        frames = rng.integers(0, 256, shape, dtype=np.uint8)
+        for dtype in (torch.float32, torch.bfloat16, torch.uint8):
+            for flip in (False, True):
+                kw = dict(flip=flip, gamma=2.2, dtype=dtype)
+                if dtype != torch.uint8:
+                    kw.update(mean=127.5, std=127.5)
+                a = _run(frames, variant="vector", **kw)
+                b = _run(frames, variant="bulk", **kw)
+                assert N.lib.bt_preprocess_last_variant() == 3
+                assert torch.equal(a.view(torch.uint8), b.view(torch.uint8))
+    out = _run(frames, variant="bulk", gamma=2.2, mean=127.5, std=127.5, out_channels=3)
+    _assert_matches(out, _oracle(frames, False, 2.2, 127.5, 127.5, "NCHW", torch.float32, 3), torch.float32)
+    with pytest.raises(N.NativeError):
+        _run(rng.integers(0, 256, (1, 4, 8, 3), dtype=np.uint8), variant="bulk")
+    with pytest.raises(N.NativeError):
+        _run(frames, variant="bulk", layout="NHWC")

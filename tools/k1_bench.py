@@ -89,7 +89,14 @@ def main():
         dict(shape=C3, dtype=torch.float32), dict(shape=C5, dtype=torch.float32),
         dict(shape=(8, 480, 640, 3), dtype=torch.float32), dict(shape=(8, 481, 641, 4), dtype=torch.float32),
     ]
-    if len(sys.argv) > 1 and sys.argv[1] == "bf16":
+    if len(sys.argv) > 1 and sys.argv[1] == "bulk":
+        cases = []
+        for shape in (C2, C4, C3, C5):
+            for variant, tune in (("vector", 0), ("bulk", 0), ("bulk", 0x200), ("bulk", 0x600), ("bulk", 0x800)):
+                cases.append(dict(shape=shape, dtype=torch.float32, variant=variant, tune=tune))
+        cases += [dict(shape=C2, dtype=torch.float32, variant=v, streams=4) for v in ("vector", "bulk")]
+        cases += [dict(shape=C4, dtype=torch.bfloat16, variant=v) for v in ("vector", "bulk")]
+    elif len(sys.argv) > 1 and sys.argv[1] == "bf16":
         cases = [dict(shape=sh, dtype=torch.bfloat16, tune=t, streams=st) for sh in (C4, C2) for t in (0, 4, 1, 44)
                  for st in ((1, 4) if sh == C2 else (1,))]
         cases += [dict(shape=(64, 1024, 1024, 1), dtype=torch.float32)]
