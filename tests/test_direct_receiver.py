@@ -163,3 +163,25 @@ def test_rejects_what_it_does_not_speak():
     rx = DirectReceiver([_free_tcp()])        # nobody there: time-out, not an error
     assert rx.recv(150) is False
     rx.close()
+
+
+def test_publisher_restart_is_picked_up_again():
+    """A publisher that goes away and comes back on the same address (a restarted Blender instance) is
+    reconnected without the consumer doing anything, as with a ZMQ socket."""
+    addr = _free_tcp()
+    first, second = _msgs(3, shape=(40, 64, 4), seed=4), _msgs(4, shape=(40, 64, 4), seed=5)
+    t = _publisher(addr, [pickle.dumps(m, protocol=3) for m in first])
+    rx = DirectReceiver([addr])
+    deadline = time.time() + 20
+    while not rx.recv(200):
+        assert time.time() < deadline
+    sch = Schema.from_message(rx.pending(), 7)
+    got = _drain(rx, sch, 3, 3)
+    t.join()                                   # the first publisher has closed its socket
+    t = _publisher(addr, [pickle.dumps(m, protocol=3) for m in second], delay=0.3)
+    got += _drain(rx, sch, 4, 4)
+    t.join()
+    rx.close()
+    ids = [(int(b["btid"][i]), int(b["frameid"][i])) for b in got for i in range(len(b["frameid"]))]
+    assert ids == [(4, 0), (4, 1), (4, 2), (5, 0), (5, 1), (5, 2), (5, 3)]
+    np.testing.assert_array_equal(got[1]["image"][3], second[3]["image"])
