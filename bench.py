@@ -177,7 +177,7 @@ def _worker_init(_):
     torch.set_num_threads(1)
 
 
-def run_cpu_reference(steps, warmup, workers, max_seconds=None):
+def run_cpu_reference(steps, warmup, workers, max_seconds=None, check_shape=True):
     """Reference CPU path on this box: synthetic publishers -> (oracle) RemoteIterableDataset port
     -> item_transform -> default_collate in `workers` DataLoader processes.  Returns
     (images/s, steps timed, seconds)."""
@@ -188,7 +188,7 @@ def run_cpu_reference(steps, warmup, workers, max_seconds=None):
         total_batches = steps + warmup
         per_worker = -(-total_batches // max(workers, 1)) + 2
         ds = stream.torch_stream_dataset(addrs, max_items=per_worker * BATCH * max(workers, 1),
-                                         item_transform=_cpu_transform, timeoutms=60000)
+                                         item_transform=(lambda it: _cpu_transform(it)), timeoutms=60000)
         dl = DataLoader(ds, batch_size=BATCH, num_workers=workers, worker_init_fn=_worker_init,
                         persistent_workers=False, prefetch_factor=4 if workers else None)
         it = iter(dl)
@@ -198,7 +198,7 @@ def run_cpu_reference(steps, warmup, workers, max_seconds=None):
         done = 0
         for _ in range(steps):
             b = next(it)
-            assert b["image"].shape == (BATCH, C, H, W)
+            assert not check_shape or b["image"].shape == (BATCH, C, H, W)
             done += 1
             if max_seconds and time.perf_counter() - t0 > max_seconds:
                 break
@@ -214,7 +214,7 @@ def reference_arm(args):
     if rank != 0:
         return 0
     cores = os.cpu_count() or 1
-    workers = max(1, min(cores - PUBLISHERS - 1, 64))
+    workers = max(1, min(cores, 64))  # all host threads: measured fastest (profiles/r1_cpu_baseline_sweep.jsonl)
     ips, done, dt = run_cpu_reference(args.steps, args.warmup, workers)
     line = {
         "impl": "reference", "metric": METRIC, "value": ips, "unit": "images/s", "n_gpus": args.gpus,
@@ -330,10 +330,12 @@ def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_th
         t0 = time.perf_counter()
         e0.record()
         images = 0
+        stamps = [t0]
         for _ in range(steps):
             b = next(it)
             st = b["image_stats"].cpu()          # D2H read of the step's result
             images += b["image"].shape[0]
+            stamps.append(time.perf_counter())
         e1.record()
         e1.synchronize()
         wall = time.perf_counter() - t0
@@ -345,6 +347,12 @@ def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_th
         it.close() if hasattr(it, "close") else None
         del it
         _ = total
+        # spread of the rate over the run: images/s in consecutive windows of 20 batches
+        win = 20
+        rates = sorted(win * BATCH / (stamps[i + win] - stamps[i]) for i in range(0, len(stamps) - win, win)
+                       if stamps[i + win] > stamps[i])
+        e2e_leg.last_spread = ({"window_batches": win, "p10": rates[len(rates) // 10], "p50": rates[len(rates) // 2],
+                                "p90": rates[(len(rates) * 9) // 10]} if rates else None)
         return images, max(sec, wall), h2d, d2h
     finally:
         stop_publishers(procs)
@@ -419,6 +427,7 @@ def ours(args):
     barrier()
     images, e2e_sec, h2d, d2h = e2e_leg(torch, btt, dev, args.steps, args.warmup, sampler, args.transport, args.receivers)
     barrier()
+    e2e_spread = getattr(e2e_leg, "last_spread", None)
     e2e_sec = max_over_ranks(e2e_sec)
     images = sum_over_ranks(images)
     e2e_value = images / e2e_sec
@@ -439,7 +448,7 @@ def ours(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
-        workers = max(1, min(cores - PUBLISHERS - 1, 64))
+        workers = max(1, min(cores, 64))  # all host threads: measured fastest (profiles/r1_cpu_baseline_sweep.jsonl)
         ips, done, dt = run_cpu_reference(steps=100000, warmup=2, workers=workers, max_seconds=15.0)
         cpu = {"value": ips, "unit": "images/s", "cores": workers, "kind": "port",
                "sample": "%d batches of %d in %.1f s through %d DataLoader workers (%d host cpus); oracle port of "
@@ -470,6 +479,7 @@ def ours(args):
                                          "achieved": large_gbs, "frac": large_gbs / peak, "ms": large_sec * 1e3}},
             "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "gbs_h2d": e2e_value * h2d_bytes_img / 1e9 / world, "pcie_h2d_measured_gbs": h2d_gbs.value,
+                    "rank0_images_per_s_spread": e2e_spread,
                     "frac_of_pcie_h2d": e2e_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value},
             "e2e_ipc": {"value": ipc_value, "unit": "images/s", "gbs_h2d": ipc_value * h2d_bytes_img / 1e9 / world,
                         "frac_of_pcie_h2d": ipc_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value,
