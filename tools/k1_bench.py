@@ -89,7 +89,11 @@ def main():
         dict(shape=C3, dtype=torch.float32), dict(shape=C5, dtype=torch.float32),
         dict(shape=(8, 480, 640, 3), dtype=torch.float32), dict(shape=(8, 481, 641, 4), dtype=torch.float32),
     ]
-    if len(sys.argv) > 1 and sys.argv[1] == "bulk":
+    if len(sys.argv) > 1 and sys.argv[1] == "lf":
+        cases = [dict(shape=sh, dtype=dt, tune=t, streams=st) for sh in (C2, (16, 480, 640, 4), C4, C5)
+                 for dt in (torch.float32, torch.bfloat16) for t in (0, 0x40000, 0x50000)
+                 for st in ((1, 4) if sh[0] <= 16 else (1,))]
+    elif len(sys.argv) > 1 and sys.argv[1] == "bulk":
         cases = []
         for shape in (C2, C4, C3, C5):
             for variant, tune in (("vector", 0), ("bulk", 0), ("bulk", 0x200), ("bulk", 0x600), ("bulk", 0x800)):
