@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define BT_ABI_VERSION 1
+#define BT_ABI_VERSION 2
 
 typedef enum bt_status {
   BT_OK = 0,
@@ -294,6 +294,12 @@ typedef struct bt_preprocess_params {
    * bt_preprocess_scratch_bytes() bytes of device memory.  NULL = off. */
   double* stats_out;
   void* stats_scratch;
+  /* Optional gather (no reference counterpart: the reference re-reads and re-decodes the file every
+   * epoch, file.py:100-108): device array of `batch` int64; batch item b is read from image
+   * src_index[b] of `src` (stride src_image_stride, or one dense frame).  Lets a sampler draw
+   * batches from frames that are resident in HBM (a recording cached on the device) with no copy
+   * pass.  The caller guarantees every index is a valid image of `src`.  NULL = item b reads image b. */
+  const int64_t* src_index;
 } bt_preprocess_params;
 
 /* The 256-entry table of offscreen.py:105-112 for one coefficient:

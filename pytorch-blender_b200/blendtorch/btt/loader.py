@@ -17,10 +17,16 @@ columns (xy, bbox, frameid, btid, depth ...) are views into the per-batch device
 cost no kernel.  Ordering and delivery follow the reference: in order per publisher with one
 receiver, unordered across receivers, every message delivered once
 (examples/datagen/Readme.md:172-177); back-pressure is the bounded queue + ZMQ high-water marks.
+
+Recordings that are replayed for many epochs can be kept in HBM (``cache='device'``): the first epoch
+goes through the pipeline above and leaves the *raw* columns (uint8 frames, 1/4 of their fp32 size)
+on the device; later epochs never touch the file, the host or PCIe -- the sampler's indices go to K1,
+which gathers its frames straight from the resident set.
 """
 import pickle
 import queue
 import threading
+import warnings
 import ctypes as C
 
 import numpy as np
@@ -46,6 +52,59 @@ def shard(seq, rank, world_size):
 
 def _torch_dtype(np_dtype):
     return torch.from_numpy(np.empty(0, dtype=np_dtype)).dtype
+
+
+class _ResidentCache:
+    """A recording kept in HBM: per column one dense device tensor whose rows are dataset indices.
+
+    Filled as a side effect of the first pass over the data (a device-to-device copy per batch on the
+    producer's stream); a row counts as present once the consumer's stream has waited for the batch
+    that carried it, so later reads on that stream are ordered after the writes."""
+
+    def __init__(self, schema, n, device, specs):
+        self.n, self.device = n, device
+        self.plan, self.cols = [], {}
+        base = torch.cuda.default_stream(device)
+        base.synchronize()                    # whatever used these blocks before is done
+        with torch.cuda.stream(base):         # not tied to a producer's stream
+            self._allocate(schema, n, device, specs)
+        self.host = {k: [None] * n for k in schema.host_keys}
+        self.present = np.zeros(n, dtype=bool)
+        self.nbytes = sum(t.numel() * t.element_size() for t in self.cols.values())
+
+    def _allocate(self, schema, n, device, specs):
+        for c in schema.columns:
+            dt = _torch_dtype(c.dtype)
+            prep = None
+            if c.key in specs:
+                shp = c.shape if len(c.shape) == 3 else c.shape + (1,)
+                prep = PreparedPreprocess(specs[c.key], shp[0], shp[1], shp[2], device)
+            self.plan.append((c.key, prep))
+            self.cols[c.key] = torch.empty((n,) + tuple(c.shape), dtype=dt, device=device)
+
+    @staticmethod
+    def bytes_needed(schema, n):
+        return n * sum(c.item_bytes for c in schema.columns)
+
+    def store(self, idx, rows):
+        """Enqueue (on the current stream) the copy of one batch's raw columns into rows `idx`."""
+        n = len(idx)
+        dense = n > 0 and int(idx[-1]) - int(idx[0]) == n - 1 and bool(np.all(np.diff(idx) == 1))
+        where = None if dense else torch.from_numpy(np.ascontiguousarray(idx, dtype=np.int64)).to(self.device)
+        for key, t in rows.items():
+            if dense:
+                self.cols[key][int(idx[0]):int(idx[0]) + n].copy_(t, non_blocking=True)
+            else:
+                self.cols[key].index_copy_(0, where, t)
+
+    def commit(self, idx, batch):
+        for k, rows in self.host.items():
+            for i, v in zip(idx, batch.get(k, ())):
+                rows[int(i)] = v
+        self.present[idx] = True
+
+    def covers(self, idx):
+        return bool(self.present[idx].all())
 
 
 class _Stager:
@@ -83,7 +142,7 @@ class _Stager:
     def ingest(self, slot, item, msg, host_rows):
         self.ring.ingest(slot, self.schema, item, msg, host_rows)
 
-    def finish(self, slot, n, host_rows):
+    def finish(self, slot, n, host_rows, cache=None, idx=None):
         sch = self.schema
         used = 0
         for _, off, ib, _, _, _ in self.plan:
@@ -94,6 +153,9 @@ class _Stager:
             self.ring.submit_batch(slot, sch, n, raw.data_ptr(), self._stream_handle)
         keep = [raw]                       # distinct storages the consumer stream must know about
         base = raw.data_ptr()
+        if cache is not None and n:
+            cache.store(idx, {key: raw[off:off + n * ib].view(dt).view((n,) + shape)
+                              for key, off, ib, dt, shape, _ in self.plan})
         for key, off, ib, dt, shape, prep in self.plan:
             if prep is None or self.keep_raw:
                 t = raw[off:off + n * ib].view(dt).view((n,) + shape)
@@ -115,7 +177,7 @@ class _Stager:
         ev.record(self.stream)
         for k in sch.host_keys:
             batch[k] = host_rows.get(k, [])
-        return batch, ev, keep
+        return batch, ev, keep, (idx if cache is not None else None)
 
     def close(self):
         self.stream.synchronize()
@@ -149,11 +211,18 @@ class DeviceLoader:
         spread over them, so socket reads of different publishers proceed in parallel.
     seed: shuffle seed (epoch number is added on every new iteration).
     keep_raw: also return the untouched uint8 frames as ``<key>_raw``.
+    cache: 'device' keeps a replayed recording resident in HBM (raw columns, i.e. uint8 frames): the
+        first epoch fills it on the way through, every later epoch is served from it -- no file, host
+        or PCIe traffic; K1 gathers the sampler's frames straight from the resident set.  Only for
+        `FileDataset` without an item_transform (a transform may differ from epoch to epoch).
+    cache_bytes: device-memory budget of the cache (default: 80 % of what is free when the layout of
+        the recording becomes known).  A recording that does not fit is replayed uncached, with a warning.
     """
 
     def __init__(self, dataset, batch_size=1, shuffle=False, drop_last=False, device="cuda",
                  preprocess=None, num_receivers=None, ring_depth=3, prefetch=2, ingest_threads=4,
-                 seed=0, keep_raw=False, io_threads=1, project=None, transport="auto"):
+                 seed=0, keep_raw=False, io_threads=1, project=None, transport="auto", cache=None,
+                 cache_bytes=None):
         self.dataset = dataset
         self.batch_size = int(batch_size)
         if self.batch_size < 1:
@@ -186,7 +255,12 @@ class DeviceLoader:
         self.transport = transport
         self._epoch = 0
         self._stagers = {}
-        self.stats = {"batches": 0, "items": 0, "bytes_h2d": 0, "kernels": 0, "compat_items": 0}
+        if cache not in (None, "device"):
+            raise ValueError("cache must be None or 'device'")
+        self.cache_mode, self.cache_bytes = cache, cache_bytes
+        self._cache, self._cache_off, self._cache_lock = None, False, threading.Lock()
+        self.stats = {"batches": 0, "items": 0, "bytes_h2d": 0, "kernels": 0, "compat_items": 0,
+                      "resident_batches": 0, "cache_bytes": 0}
         if isinstance(dataset, RemoteIterableDataset):
             if shuffle:
                 raise ValueError("iterable datasets do not support shuffle")
@@ -195,6 +269,8 @@ class DeviceLoader:
             self._mode = "replay"
         else:
             raise TypeError("DeviceLoader takes a btt.RemoteIterableDataset or a btt.FileDataset")
+        if cache is not None and (self._mode != "replay" or dataset.has_custom_item()):
+            raise ValueError("cache='device' is for FileDataset replay without an item_transform")
 
     def __len__(self):
         if self._mode == "replay":
@@ -245,10 +321,33 @@ class DeviceLoader:
             stager.close()
 
     def close(self):
-        """Release pinned rings and streams kept between epochs."""
+        """Release pinned rings and streams kept between epochs, and the resident recording."""
         for _, st in self._stagers.values():
             st.close()
         self._stagers = {}
+        if self._cache is not None:
+            torch.cuda.synchronize(self.device)    # readers of the resident rows may still be running
+            self._cache = None
+
+    def _resident(self, schema):
+        """The cache the producers fill, created when the first producer knows the layout."""
+        if self.cache_mode is None or self._cache_off:
+            return None
+        with self._cache_lock:
+            if self._cache is None and not self._cache_off:
+                n = len(self.dataset)
+                need = _ResidentCache.bytes_needed(schema, n)
+                budget = self.cache_bytes
+                if budget is None:
+                    budget = int(torch.cuda.mem_get_info(self.device)[0] * 0.8)
+                if need > budget:
+                    self._cache_off = True
+                    warnings.warn("recording needs %d bytes on the device, cache budget is %d: replaying uncached"
+                                  % (need, budget))
+                    return None
+                self._cache = _ResidentCache(schema, n, self.device, self.specs)
+                self.stats["cache_bytes"] = self._cache.nbytes
+            return self._cache
 
     def __del__(self):
         try:
@@ -256,8 +355,8 @@ class DeviceLoader:
         except Exception:
             pass
 
-    def _emit(self, out_q, stop, stager, slot, n, host_rows):
-        item = stager.finish(slot, n, host_rows)
+    def _emit(self, out_q, stop, stager, slot, n, host_rows, cache=None, idx=None):
+        item = stager.finish(slot, n, host_rows, cache, idx)
         self.stats["bytes_h2d"] += stager.item_bytes * n
         while not stop.is_set():
             try:
@@ -481,13 +580,70 @@ class DeviceLoader:
                     if done != len(idx):  # at least one message needs the compatibility decode
                         for i, (f, l) in enumerate(zip(fidx, local)):
                             stager.ingest(slot, i, readers[f].raw(int(l)), host_rows)
-                if not self._emit(out_q, stop, stager, slot, len(idx), host_rows):
+                cache = None if custom else self._resident(stager.schema)
+                if not self._emit(out_q, stop, stager, slot, len(idx), host_rows, cache, idx):
                     return
         except BaseException as e:
             out_q.put(e)
         finally:
             self._retire(stager)
             out_q.put(_DONE)
+
+    def _resident_epoch(self, order):
+        """An epoch served from HBM: per batch one K1 launch that gathers its frames from the resident
+        set by index (other columns: index_select), all on the consumer's current stream."""
+        cache, B, dev = self._cache, self.batch_size, self.device
+        with torch.cuda.device(dev):
+            order_dev = torch.from_numpy(np.ascontiguousarray(order, dtype=np.int64)).to(dev)
+            for _, st in self._stagers.values():   # the streams that wrote the resident rows
+                torch.cuda.current_stream(dev).wait_stream(st.stream)
+            # annotation columns are small: gather them for the whole epoch at once, batches are views
+            whole = {}
+            for key, prep in cache.plan:
+                store = cache.cols[key]
+                if (prep is None or self.keep_raw) and store[:1].numel() * store.element_size() * len(order) <= (64 << 20):
+                    whole[key] = store.index_select(0, order_dev)
+            seen_stream = torch.cuda.current_stream(dev)
+        kernels = 0
+        try:
+            for start in range(0, len(order), B):
+                idx = order_dev[start:start + B]
+                n = idx.numel()
+                if n < B and self.drop_last:
+                    break
+                with torch.cuda.device(dev):
+                    cur = torch.cuda.current_stream(dev)
+                    if cur != seen_stream:             # the consumer moved to another stream
+                        seen_stream = cur
+                        for t in (order_dev, *whole.values()):
+                            t.record_stream(cur)
+                    handle = C.c_void_p(cur.cuda_stream)
+                    batch = {}
+                    for key, prep in cache.plan:
+                        store = cache.cols[key]
+                        if prep is None or self.keep_raw:
+                            t = whole[key][start:start + B] if key in whole else store.index_select(0, idx)
+                        if prep is not None:
+                            out, stats = prep.run(store.data_ptr(), n, handle, idx.data_ptr())
+                            kernels += 1
+                            if stats is not None:
+                                batch[key + "_stats"] = stats
+                            if self.keep_raw:
+                                batch[key + "_raw"] = t
+                            t = out
+                        batch[key] = t
+                    for pj in self.projections:
+                        pj.apply(batch, dev)
+                        kernels += 1
+                host_idx = order[start:start + B]
+                for k, rows in cache.host.items():
+                    batch[k] = [rows[int(i)] for i in host_idx]
+                self.stats["batches"] += 1
+                self.stats["resident_batches"] += 1
+                self.stats["items"] += n
+                yield batch
+        finally:
+            self.stats["kernels"] += kernels
 
     # ---- consumer ---------------------------------------------------------------------------
     def _replay_producers(self):
@@ -496,6 +652,14 @@ class DeviceLoader:
         return max(1, min(n, 8))
 
     def __iter__(self):
+        if self._cache is not None:
+            self._epoch += 1                       # the order of the epoch that starts now
+            order = self._replay_order()
+            usable = len(order) - (len(order) % self.batch_size if self.drop_last else 0)
+            if self._cache.covers(order[:usable]):
+                yield from self._resident_epoch(order)
+                return
+            self._epoch -= 1
         stop = threading.Event()
         if self._mode == "stream":
             n_prod, target = self.num_receivers, self._stream_producer
@@ -534,11 +698,13 @@ class DeviceLoader:
                     continue
                 if isinstance(item, BaseException):
                     raise item
-                batch, ev, keep = item
+                batch, ev, keep, idx = item
                 cur = torch.cuda.current_stream(self.device)
                 cur.wait_event(ev)
                 for t in keep:
                     t.record_stream(cur)
+                if idx is not None and self._cache is not None:
+                    self._cache.commit(idx, batch)
                 self.stats["batches"] += 1
                 self.stats["items"] += len(batch["btid"]) if "btid" in batch else next((len(v) for v in batch.values()), 0)
                 yield batch

@@ -57,7 +57,8 @@ class PreprocessParams(C.Structure):
                 ("use_gamma", C.c_int32), ("use_norm", C.c_int32), ("variant", C.c_int32), ("reserved", C.c_int32),
                 ("src_image_stride", C.c_uint64),
                 ("mean", C.c_float * 4), ("stdev", C.c_float * 4), ("gamma_lut", C.c_uint8 * 256),
-                ("stats_out", C.c_void_p), ("stats_scratch", C.c_void_p)]
+                ("stats_out", C.c_void_p), ("stats_scratch", C.c_void_p),
+                ("src_index", C.c_void_p)]
 
 
 class ProjectParams(C.Structure):

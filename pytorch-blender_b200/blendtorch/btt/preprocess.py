@@ -76,8 +76,11 @@ def _stream_handle(stream):
     return C.c_void_p(stream.cuda_stream)
 
 
-def preprocess_images(src, spec, out=None, stream=None, stats_out=None, _scratch=None):
+def preprocess_images(src, spec, out=None, stream=None, stats_out=None, _scratch=None, index=None):
     """Run K1 on `src`, a CUDA uint8 tensor (B,H,W,C) or (B,H,W), per `spec`.
+
+    index: optional CUDA int64 tensor (n,): output item i is made from ``src[index[i]]`` -- a batch
+        drawn from frames resident on the device, without a gather pass.
 
     Returns the output tensor, or (output, stats) when ``spec.stats``; stats is a
     (C_out, 2) float64 CUDA tensor [sum, sum of squares].  Work is enqueued on `stream`
@@ -96,6 +99,13 @@ def preprocess_images(src, spec, out=None, stream=None, stats_out=None, _scratch
         raise ValueError("channels must be 1..4")
     if src.stride(3) != 1 or src.stride(2) != Cn or src.stride(1) != W * Cn:
         src = src.contiguous()
+    n_src = B
+    if index is not None:
+        if not index.is_cuda or index.dtype != torch.int64 or index.dim() != 1 or not index.is_contiguous():
+            raise ValueError("index must be a contiguous 1-d CUDA int64 tensor")
+        if B == 0 and index.numel():
+            raise IndexError("index into an empty set of frames")
+        B = index.numel()
     cout = spec.out_channels or Cn
     if not 1 <= cout <= Cn:
         raise ValueError("out_channels must be within 1..channels")
@@ -124,7 +134,8 @@ def preprocess_images(src, spec, out=None, stream=None, stats_out=None, _scratch
     p.use_norm = int(spec.mean is not None or spec.std is not None)
     p.variant = VARIANTS[spec.variant]
     p.reserved = int(spec.tune)
-    p.src_image_stride = src.stride(0) if B > 1 else 0
+    p.src_image_stride = src.stride(0) if n_src > 1 else 0
+    p.src_index = index.data_ptr() if index is not None else None
     mean, std = _per_channel(spec.mean, 0.0), _per_channel(spec.std, 1.0)
     for c in range(4):
         p.mean[c], p.stdev[c] = mean[c], std[c]
@@ -184,9 +195,10 @@ class PreparedPreprocess:
     def out_shape(self, n):
         return (n, self.cout, self.h, self.w) if self.spec.layout == "NCHW" else (n, self.h, self.w, self.cout)
 
-    def run(self, src_ptr, n, stream_handle):
-        """Launch on `n` dense frames at device address `src_ptr`; allocations come from torch's
-        *current* stream, which the caller has set to the stream behind `stream_handle`."""
+    def run(self, src_ptr, n, stream_handle, index_ptr=None):
+        """Launch on `n` dense frames at device address `src_ptr` (with `index_ptr`, the device
+        address of `n` int64: on frames ``index[i]`` of the dense set at `src_ptr`); allocations come
+        from torch's *current* stream, which the caller has set to the stream behind `stream_handle`."""
         out = torch.empty(self.out_shape(n), dtype=self.spec.dtype, device=self.device)
         stats = None
         p = self.params
@@ -196,5 +208,6 @@ class PreparedPreprocess:
         if n == 0:
             return out, (stats.zero_() if stats is not None else None)
         p.src, p.dst, p.batch = src_ptr, out.data_ptr(), n
+        p.src_index = index_ptr
         N.check(N.lib.bt_preprocess_launch(self._ref, stream_handle))
         return out, stats

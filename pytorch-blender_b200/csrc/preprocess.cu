@@ -36,6 +36,7 @@ struct K1Args {
   uint32_t flip, use_gamma, use_norm;
   uint32_t flags;             // bit 0: k1_planar issues its first loads before building the table
   uint64_t src_image_stride;  // bytes
+  const long long* src_index; // optional [B]: which source image feeds batch item b (nullptr: b itself)
   float mean[4];
   float stdev[4];
   uint8_t gamma_lut[256];
@@ -43,6 +44,14 @@ struct K1Args {
   unsigned int* ticket;   // arrival counter, zero on entry, reset to zero on exit
   double* stats_out;      // [Cout][2]
 };
+
+// Byte offset of the source image that feeds batch item `b`: dense batches read image b, gathered
+// batches (frames resident in HBM, picked by a sampler) read image src_index[b].  The test is on a
+// kernel parameter, i.e. uniform; the index array is a few hundred bytes and stays in L1.
+__device__ __forceinline__ uint64_t src_image_off(const K1Args& a, uint32_t b) {
+  const uint64_t img = a.src_index ? (uint64_t)__ldg(a.src_index + b) : (uint64_t)b;
+  return img * a.src_image_stride;
+}
 
 // ---- output-type helpers -----------------------------------------------------------------
 template <typename T> struct OutT;
@@ -193,7 +202,7 @@ __global__ void __launch_bounds__(kThreads) k1_generic(K1Args a) {
     if (CHW) { c = r / (a.H * a.W); uint32_t p = r - c * a.H * a.W; y = p / a.W; x = p - y * a.W; }
     else { uint32_t p = r / a.Cout; c = r - p * a.Cout; y = p / a.W; x = p - y * a.W; }
     uint32_t sy = a.flip ? a.H - 1 - y : y;
-    uint8_t v = a.src[(uint64_t)b * a.src_image_stride + ((uint64_t)sy * a.W + x) * a.C + c];
+    uint8_t v = a.src[src_image_off(a, b) + ((uint64_t)sy * a.W + x) * a.C + c];
     T o = lut[c * 256 + v];
     dst[i] = o;
     if (STATS) {
@@ -280,7 +289,7 @@ __global__ void __launch_bounds__(kThreads) k1_planar(K1Args a, PlanarGeom g) {
         const uint32_t b = fdiv(row, g.rows);
         const uint32_t y = row - b * g.rows.div;
         const uint32_t sy = a.flip ? a.H - 1 - y : y;
-        const uint8_t* sp = a.src + (uint64_t)b * a.src_image_stride + ((uint64_t)sy * a.W + (uint64_t)ux * PPT) * C;
+        const uint8_t* sp = a.src + src_image_off(a, b) + ((uint64_t)sy * a.W + (uint64_t)ux * PPT) * C;
 #pragma unroll
         for (int l = 0; l < UB / LW; ++l) ld_words<LW>(sp + l * LW, &in[j][l * (LW / 4)]);
         out_off[j] = ((uint64_t)b * a.Cout) * plane + (uint64_t)y * a.W + (uint64_t)ux * PPT;
@@ -372,7 +381,7 @@ __global__ void __launch_bounds__(kThreads) k1_bulk(K1Args a, BulkGeom g) {
     const uint32_t sy = a.flip ? a.H - 1 - y : y;
     const uint32_t off = sx * kBulkSegBytes;
     bytes = row_bytes - off < (uint32_t)kBulkSegBytes ? row_bytes - off : (uint32_t)kBulkSegBytes;
-    src = a.src + (uint64_t)b * a.src_image_stride + (uint64_t)sy * row_bytes + off;
+    src = a.src + src_image_off(a, b) + (uint64_t)sy * row_bytes + off;
     out_off = ((uint64_t)b * a.Cout) * plane + (uint64_t)y * a.W + (off >> 2);
   };
 
@@ -468,7 +477,7 @@ __global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a, PlanarGeom 
         const uint32_t b = fdiv(row, g.rows);
         const uint32_t y = row - b * g.rows.div;
         const uint32_t sy = a.flip ? a.H - 1 - y : y;
-        ld_words<LW>(a.src + (uint64_t)b * a.src_image_stride + (uint64_t)sy * row_bytes + (uint64_t)ux * IB, in[j]);
+        ld_words<LW>(a.src + src_image_off(a, b) + (uint64_t)sy * row_bytes + (uint64_t)ux * IB, in[j]);
         out_off[j] = (uint64_t)row * row_bytes + (uint64_t)ux * IB;
         phase[j] = (ux * (uint32_t)IB) % C;
       }
@@ -526,7 +535,7 @@ __global__ void __launch_bounds__(kThreads) k1_pixel(K1Args a, PlanarGeom g) {
         const uint32_t b = fdiv(row, g.rows);
         const uint32_t y = row - b * g.rows.div;
         const uint32_t sy = a.flip ? a.H - 1 - y : y;
-        const uint8_t* sp = a.src + (uint64_t)b * a.src_image_stride + ((uint64_t)sy * a.W + x) * C;
+        const uint8_t* sp = a.src + src_image_off(a, b) + ((uint64_t)sy * a.W + x) * C;
         if constexpr (C == 4) {
           ld_words<4>(sp, &px[j]);
         } else {
@@ -803,6 +812,7 @@ int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) {
   const uint64_t dense = (uint64_t)p->height * p->width * p->channels;
   a.src_image_stride = p->src_image_stride ? p->src_image_stride : dense;
   if (a.src_image_stride < dense) return bt::fail(BT_E_INVALID, "src_image_stride smaller than one frame");
+  a.src_index = reinterpret_cast<const long long*>(p->src_index);
   memcpy(a.mean, p->mean, sizeof a.mean);
   memcpy(a.stdev, p->stdev, sizeof a.stdev);
   memcpy(a.gamma_lut, p->gamma_lut, 256);

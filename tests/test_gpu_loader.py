@@ -289,3 +289,75 @@ def test_stream_through_the_direct_receiver():
     finally:
         for p in procs:
             p.join(timeout=10)
+
+
+def _epochs(dl, n):
+    out = []
+    for _ in range(n):
+        out.append([{k: (v.cpu() if torch.is_tensor(v) else v) for k, v in b.items()} for b in dl])
+    return out
+
+
+def _same_batches(a, b):
+    assert len(a) == len(b)
+    for x, y in zip(a, b):
+        assert set(x) == set(y)
+        for k in x:
+            if torch.is_tensor(x[k]):
+                assert x[k].dtype == y[k].dtype and x[k].shape == y[k].shape, k
+                assert torch.equal(x[k].view(torch.uint8), y[k].view(torch.uint8)), k
+            else:
+                assert x[k] == y[k], k
+
+
+@pytest.mark.parametrize("shuffle,drop_last", [(False, False), (True, False), (True, True)])
+def test_resident_recording_serves_later_epochs_identically(golden_dir, shuffle, drop_last):
+    """cache='device': epoch 1 goes through the pinned pipeline and leaves the raw columns in HBM; epochs
+    2.. are gathered from there by K1 -- same batches, bit for bit, as the uncached loader with the same
+    seed (which re-reads the files every epoch like the reference, file.py:100-108)."""
+    ds = btt.FileDataset(str(golden_dir / "rec_small"))
+    kw = dict(batch_size=4, device=DEV, shuffle=shuffle, drop_last=drop_last, seed=11, keep_raw=True,
+              preprocess=btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5, stats=True))
+    plain = btt.DeviceLoader(ds, **kw)
+    cached = btt.DeviceLoader(ds, cache="device", **kw)
+    want, got = _epochs(plain, 4), _epochs(cached, 4)
+    for e in range(4):
+        _same_batches(want[e], got[e])
+    st = cached.stats
+    assert st["cache_bytes"] == 11 * (12 * 16 * 4 + 8 * 2 * 8 + 8 + 8)
+    if drop_last and shuffle:
+        # 3 of 11 frames are dropped each epoch: epochs stay on the pipeline until every frame an
+        # epoch needs has been seen
+        assert 0 <= st["resident_batches"] <= 6
+    else:
+        assert st["resident_batches"] == 3 * len(want[0])
+        assert st["bytes_h2d"] == plain.stats["bytes_h2d"] // 4     # only the first epoch crossed PCIe
+    plain.close()
+    cached.close()
+
+
+def test_resident_recording_limits_and_projection(tmp_path):
+    names = S.write_recordings(str(tmp_path / "c3"), 3, n_files=2, frames_per_file=5, h=24, w=32)
+    assert len(names) == 2
+    ds = btt.FileDataset(str(tmp_path / "c3"))
+    from oracle import camera as ocam
+    cam = btt.Camera(ocam.view_looking_down_z(0.0), ocam.blender_perspective((24, 32), lens=35.0), (24, 32), device=DEV)
+    kw = dict(batch_size=3, device=DEV, shuffle=True, seed=2,
+              preprocess=[btt.Preprocess(mean=127.5, std=127.5, dtype=torch.bfloat16)],
+              project=btt.Projection("corners", cam, xy_key="xy", bbox_key="bbox", depth_key="z"))
+    plain, cached = btt.DeviceLoader(ds, **kw), btt.DeviceLoader(ds, cache="device", **kw)
+    want, got = _epochs(plain, 3), _epochs(cached, 3)
+    for e in range(3):
+        _same_batches(want[e], got[e])
+    assert cached.stats["resident_batches"] == 2 * len(want[0])
+    # a budget the recording does not fit: replay stays uncached, and says so
+    small = btt.DeviceLoader(ds, cache="device", cache_bytes=1000, **kw)
+    with pytest.warns(UserWarning, match="replaying uncached"):
+        first = _epochs(small, 1)
+    _same_batches(_epochs(btt.DeviceLoader(ds, **kw), 1)[0], first[0])
+    assert small.stats["resident_batches"] == 0 and small.stats["cache_bytes"] == 0
+    # not for streams, not with an item_transform
+    with pytest.raises(ValueError):
+        btt.DeviceLoader(btt.FileDataset(str(tmp_path / "c3"), item_transform=lambda x: x), device=DEV, cache="device")
+    with pytest.raises(ValueError):
+        btt.DeviceLoader(btt.RemoteIterableDataset(["tcp://127.0.0.1:1"]), device=DEV, cache="device")

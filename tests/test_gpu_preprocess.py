@@ -211,3 +211,39 @@ def test_bulk_async_variant_matches_the_register_variant():
         _run(rng.integers(0, 256, (1, 4, 8, 3), dtype=np.uint8), variant="bulk")
     with pytest.raises(N.NativeError):
         _run(frames, variant="bulk", layout="NHWC")
+
+
+def test_gather_index_matches_oracle_on_every_variant():
+    """`index=` draws the batch from frames resident on the device: output item i must be the oracle's
+    transform of frame index[i] (repeats, reversed order, a subset), bit for bit, on every kernel."""
+    from blendtorch.btt import native as N
+    rng = np.random.default_rng(33)
+    cases = [((9, 12, 16, 4), "auto", 2), ((9, 12, 16, 4), "generic", 1), ((6, 8, 1028, 4), "bulk", 3),
+             ((7, 7, 5, 4), "auto", 4), ((5, 9, 16, 3), "auto", None), ((4, 5, 16, 1), "auto", None)]
+    for shape, variant, ran in cases:
+        frames = rng.integers(0, 256, shape, dtype=np.uint8)
+        src = torch.from_numpy(frames).to(DEV)
+        idx = np.concatenate([rng.permutation(shape[0]), [0, 0, shape[0] - 1]])
+        index = torch.from_numpy(idx).to(DEV)
+        for dtype, layout, flip in ((torch.float32, "NCHW", True), (torch.bfloat16, "NCHW", False),
+                                    (torch.float32, "NHWC", True), (torch.uint8, "NHWC", False)):
+            if variant == "bulk" and layout == "NHWC":
+                continue
+            kw = dict(flip=flip, gamma=2.2, layout=layout, dtype=dtype, variant=variant)
+            if dtype != torch.uint8:
+                kw.update(mean=127.5, std=127.5)
+            out = btt.preprocess_images(src, btt.Preprocess(**kw), index=index)
+            torch.cuda.synchronize()
+            if ran is not None:
+                assert N.lib.bt_preprocess_last_variant() == ran, (shape, variant, layout)
+            assert out.shape[0] == len(idx)
+            exp = _oracle(frames[idx], flip, 2.2, kw.get("mean"), kw.get("std"), layout, dtype)
+            _assert_matches(out, exp, dtype)
+    # statistics follow the gathered items, and an empty index gives an empty batch
+    out, st = btt.preprocess_images(src, btt.Preprocess(mean=127.5, std=127.5, stats=True), index=index)
+    dense, st2 = btt.preprocess_images(src[index], btt.Preprocess(mean=127.5, std=127.5, stats=True))
+    assert torch.equal(out, dense) and torch.equal(st, st2)
+    none = btt.preprocess_images(src, btt.Preprocess(), index=index[:0])
+    assert none.shape[0] == 0
+    with pytest.raises(ValueError):
+        btt.preprocess_images(src, btt.Preprocess(), index=index.to(torch.int32))
