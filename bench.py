@@ -490,7 +490,9 @@ def ours(args):
                                      "producer -> shared memory -> DMA, no consumer-side CPU copy; not the reference's "
                                      "pickle wire, reported beside e2e, not instead of it" % args.shm_slots,
                              "receivers": args.shm_receivers},
-            "gpu_launches": args.steps, "gpu_launches_e2e": args.steps,
+            "gpu_launches": args.steps,
+            # e2e batches carry statistics (the step's result that is read back): K1 + the fold kernel of its rows
+            "gpu_launches_e2e": 2 * args.steps,
             "clocks": clocks,
             "cpu_baseline": cpu,
             "host": {"cpus": os.cpu_count()},

@@ -291,7 +291,8 @@ typedef struct bt_preprocess_params {
   /* Optional per-batch statistics of the values written (north_star "optional per-batch
    * stats"; no reference counterpart): stats_out[c*2+0] = sum, [c*2+1] = sum of squares, as
    * float64, deterministic (fixed reduction order).  Needs `stats_scratch` of
-   * bt_preprocess_scratch_bytes() bytes of device memory.  NULL = off. */
+   * bt_preprocess_scratch_bytes() bytes of device memory (uninitialised is fine); the sums are
+   * added up by one or two small kernels enqueued behind K1 on the same stream.  NULL = off. */
   double* stats_out;
   void* stats_scratch;
   /* Optional gather (no reference counterpart: the reference re-reads and re-decodes the file every
@@ -307,14 +308,16 @@ typedef struct bt_preprocess_params {
 int bt_build_gamma_lut(double coeff, uint8_t lut[256]);
 uint64_t bt_preprocess_scratch_bytes(const bt_preprocess_params* p);
 int bt_preprocess_launch(const bt_preprocess_params* p, void* stream);
-/* How many kernels the last bt_preprocess_launch on this thread enqueued and which variant ran. */
+/* Which variant the last bt_preprocess_launch on this thread ran, and how many kernels it enqueued
+ * (K1, plus one or two small fold kernels when statistics are on). */
 int bt_preprocess_last_variant(void);
+int bt_preprocess_last_kernels(void);
 
 /* K1 with per-batch statistics for callers that cannot allocate device memory.
  * (No counterpart in the reference: it never touches the device.)
  *
  * Same semantics and same kernel as bt_preprocess_launch with `stats_out` set, but the scratch
- * the statistics need (per-CTA partial sums + an arrival counter) is a fixed array compiled into
+ * the statistics need (one row of partial sums per CTA) is a fixed array compiled into
  * the library instead of caller memory, and the call performs no cudaMalloc / cudaFree or any
  * other allocating routine.  Meant for hosts that give a plug-in a fixed device-memory budget,
  * for ingest loops that may not call an allocator after start-up, and for processes sharing a
@@ -327,9 +330,9 @@ int bt_preprocess_last_variant(void);
  *  - The array costs 76 032 bytes on every GPU that loads the library, until the process exits.
  *  - The first call on each device resolves the array's device address (and, like any first
  *    launch, loads the kernels); make that first call before starting any stream capture.
- *  - All calls on a device share the one array.  The arrival counter is zeroed on `stream` before
- *    every launch and the partial sums are rewritten before they are read, so back-to-back calls
- *    on one stream are fine; calls whose kernels can overlap on the GPU (different streams or
+ *  - All calls on a device share the one array.  Nothing in it has to start at zero: the partial
+ *    sums are written by each call's kernel before its fold reads them, so back-to-back calls on
+ *    one stream are fine; calls whose kernels can overlap on the GPU (different streams or
  *    threads without ordering between them) race on it and give wrong statistics. */
 int bt_preprocess_stats_static(const bt_preprocess_params* p, void* stream);
 

@@ -161,7 +161,7 @@ class _Stager:
                 t = raw[off:off + n * ib].view(dt).view((n,) + shape)
             if prep is not None:
                 out, stats = prep.run(base + off, n, self._stream_handle)
-                self.kernels += 1
+                self.kernels += prep.last_kernels
                 keep.append(out)
                 if stats is not None:
                     batch[key + "_stats"] = stats
@@ -625,7 +625,7 @@ class DeviceLoader:
                             t = whole[key][start:start + B] if key in whole else store.index_select(0, idx)
                         if prep is not None:
                             out, stats = prep.run(store.data_ptr(), n, handle, idx.data_ptr())
-                            kernels += 1
+                            kernels += prep.last_kernels
                             if stats is not None:
                                 batch[key + "_stats"] = stats
                             if self.keep_raw:

@@ -205,9 +205,13 @@ class PreparedPreprocess:
         if self.spec.stats:
             stats = torch.empty((self.cout, 2), dtype=torch.float64, device=self.device)
             p.stats_out = stats.data_ptr()
+        self.last_kernels = 0
         if n == 0:
             return out, (stats.zero_() if stats is not None else None)
         p.src, p.dst, p.batch = src_ptr, out.data_ptr(), n
         p.src_index = index_ptr
         N.check(N.lib.bt_preprocess_launch(self._ref, stream_handle))
+        self.last_kernels = 2 if stats is not None else 1   # K1 + the fold of its statistics rows
+        if stats is not None:
+            self.last_kernels = N.lib.bt_preprocess_last_kernels()
         return out, stats

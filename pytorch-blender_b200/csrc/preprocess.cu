@@ -41,7 +41,6 @@ struct K1Args {
   float stdev[4];
   uint8_t gamma_lut[256];
   double* partials;       // [gridDim.x][kMaxC][2] when stats are on
-  unsigned int* ticket;   // arrival counter, zero on entry, reset to zero on exit
   double* stats_out;      // [Cout][2]
 };
 
@@ -118,27 +117,92 @@ struct StatAcc {
   }
 };
 
-__device__ __forceinline__ double shfl_down_f64(double v, int d) {
+__device__ __forceinline__ double shfl_xor_f64(double v, int d) {
   int lo = __double2loint(v), hi = __double2hiint(v);
-  lo = __shfl_down_sync(0xffffffffu, lo, d);
-  hi = __shfl_down_sync(0xffffffffu, hi, d);
+  lo = __shfl_xor_sync(0xffffffffu, lo, d);
+  hi = __shfl_xor_sync(0xffffffffu, hi, d);
   return __hiloint2double(hi, lo);
 }
 
-// warp shuffle -> shared -> one partial row per CTA -> last CTA folds the rows in index order.
+// ---- the fold of the per-CTA rows: its own small kernel -------------------------------------------
+// The producing kernel only writes one row of partial sums per CTA; no fence, no arrival counter, no
+// "last CTA" tail.  (Measured: with the fold inside the producer every CTA paid a __threadfence -- a
+// wait for all of its streamed output to be acknowledged -- plus an atomic round trip before it
+// could retire, which cost a one-pass grid more than the whole reduction is worth.)  The kernel
+// boundary orders the rows before their readers, and programmatic dependent launch hides the launch.
+constexpr int kFoldThreads = 1024;
+constexpr int kFoldRowsPerCta = 1024;   // rows a CTA folds when the fold is spread over several CTAs
+constexpr int kFoldDirectMax = 2048;    // up to this many rows a single CTA folds them all
+
+// out[cta][pair] = sum over the CTA's rows, fixed order: 256 threads per channel pair take rows
+// grp, grp+256, ... (16-byte loads, four in flight), a shuffle tree adds the lanes of each warp and
+// one thread adds the pair's eight warps in order.
+__global__ void __launch_bounds__(kFoldThreads) k1_fold(const double* rows, unsigned n, unsigned rows_per_cta,
+                                                        double* out, unsigned out_pairs) {
+  __shared__ double warp_sum[kMaxC][kFoldThreads / 32 / kMaxC][2];
+  asm volatile("griddepcontrol.wait;" ::: "memory");   // the rows of the producer are complete and visible
+  asm volatile("griddepcontrol.launch_dependents;");
+  const unsigned first = blockIdx.x * rows_per_cta;
+  const unsigned last = first + rows_per_cta < n ? first + rows_per_cta : n;
+  const int pair = threadIdx.x >> 8, grp = threadIdx.x & 255, lane = threadIdx.x & 31, w = (threadIdx.x >> 5) & 7;
+  constexpr int kInFlight = 4;
+  double ts = 0.0, tq = 0.0;
+  for (unsigned b0 = first + grp; b0 < last; b0 += 256 * kInFlight) {
+    double2 r[kInFlight];
+#pragma unroll
+    for (int j = 0; j < kInFlight; ++j) {
+      const unsigned b = b0 + 256 * j;
+      r[j] = b < last ? __ldcg(reinterpret_cast<const double2*>(rows + ((size_t)b * kMaxC + pair) * 2)) : make_double2(0.0, 0.0);
+    }
+#pragma unroll
+    for (int j = 0; j < kInFlight; ++j) { ts += r[j].x; tq += r[j].y; }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    ts += shfl_xor_f64(ts, d);
+    tq += shfl_xor_f64(tq, d);
+  }
+  if (lane == 0) { warp_sum[pair][w][0] = ts; warp_sum[pair][w][1] = tq; }
+  __syncthreads();
+  if (grp < 2 && (unsigned)pair < out_pairs) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < kFoldThreads / 32 / kMaxC; ++k) t += warp_sum[pair][k][grp];
+    out[((size_t)blockIdx.x * out_pairs + pair) * 2 + grp] = t;
+  }
+}
+
+// warp shuffle -> shared -> one partial row per CTA (k1_fold adds the rows in index order).
 __device__ void finish_stats(const K1Args& a, StatAcc& acc) {
   __shared__ double red[kThreads / 32][kMaxC][2];
-  __shared__ bool last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // Warp reduction of the 8 values (s0,q0,..,s3,q3) with 9 double shuffles instead of 40: every
+  // round halves both the lanes that share a value and the values a lane still carries
+  // (exchange with lane^16: keep 4, lane^8: keep 2, lane^4: keep 1), then two plain rounds.
+  // Lane l ends up owning value ((l>>4)&1)*4 + ((l>>3)&1)*2 + ((l>>2)&1).  Fixed order: deterministic.
+  {
+    double v[8], w4[4], w2[2];
 #pragma unroll
-  for (int c = 0; c < kMaxC; ++c) {
-    double s = acc.s[c], q = acc.q[c];
+    for (int c = 0; c < kMaxC; ++c) { v[2 * c] = acc.s[c]; v[2 * c + 1] = acc.q[c]; }
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) {
-      s += shfl_down_f64(s, d);
-      q += shfl_down_f64(q, d);
+    for (int i = 0; i < 4; ++i) {
+      const double keep = h16 ? v[i + 4] : v[i], send = h16 ? v[i] : v[i + 4];
+      w4[i] = keep + shfl_xor_f64(send, 16);
     }
-    if (lane == 0) { red[warp][c][0] = s; red[warp][c][1] = q; }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const double keep = h8 ? w4[i + 2] : w4[i], send = h8 ? w4[i] : w4[i + 2];
+      w2[i] = keep + shfl_xor_f64(send, 8);
+    }
+    const double keep = h4 ? w2[1] : w2[0], send = h4 ? w2[0] : w2[1];
+    double t = keep + shfl_xor_f64(send, 4);
+    t += shfl_xor_f64(t, 2);
+    t += shfl_xor_f64(t, 1);
+    if ((lane & 3) == 0) {
+      const int idx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+      red[warp][idx >> 1][idx & 1] = t;
+    }
   }
   __syncthreads();
   if (threadIdx.x < kMaxC * 2) {
@@ -147,41 +211,6 @@ __device__ void finish_stats(const K1Args& a, StatAcc& acc) {
     for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w][c][k];
     a.partials[((size_t)blockIdx.x * kMaxC + c) * 2 + k] = t;
   }
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) last = atomicAdd(a.ticket, 1u) == gridDim.x - 1;
-  __syncthreads();
-  if (!last) return;
-  __threadfence();
-  // Fold the rows with the whole CTA, still in a fixed order: thread t owns value (t & 7) of rows
-  // t>>3, t>>3 + 32, ... (coalesced 2 KB per step), then lane groups are folded in index order.
-  {
-    constexpr int kVals = kMaxC * 2;            // 8 doubles per row
-    constexpr int kGroups = kThreads / kVals;   // 32 row groups
-    const int v = threadIdx.x & (kVals - 1), grp = threadIdx.x >> 3;
-    double t = 0.0;
-    constexpr int kInFlight = 8;                // independent loads per step: the fold is latency-bound
-    for (unsigned b0 = grp; b0 < gridDim.x; b0 += kGroups * kInFlight) {
-      double r[kInFlight];
-#pragma unroll
-      for (int j = 0; j < kInFlight; ++j) {
-        const unsigned b = b0 + j * kGroups;
-        r[j] = b < gridDim.x ? __ldcg(&a.partials[(size_t)b * kVals + v]) : 0.0;
-      }
-#pragma unroll
-      for (int j = 0; j < kInFlight; ++j) t += r[j];
-    }
-    __shared__ double grp_sum[kGroups][kVals];
-    grp_sum[grp][v] = t;
-    __syncthreads();
-    if (threadIdx.x < kVals) {
-      double s = 0.0;
-      for (int g2 = 0; g2 < kGroups; ++g2) s += grp_sum[g2][threadIdx.x];
-      const int c = threadIdx.x >> 1, k = threadIdx.x & 1;
-      if (c < (int)a.Cout) a.stats_out[c * 2 + k] = s;
-    }
-  }
-  if (threadIdx.x == 0) *a.ticket = 0;  // ready for the next launch
 }
 
 // ---- variant 1: generic scalar (any shape) -----------------------------------------------
@@ -248,7 +277,7 @@ __device__ __forceinline__ void ld_words(const uint8_t* p, uint32_t* w) {
 }
 
 template <typename T, int C, int PPT, int UNROLL, bool STATS>
-__global__ void __launch_bounds__(kThreads) k1_planar(K1Args a, PlanarGeom g) {
+__global__ void __launch_bounds__(kThreads, (STATS || sizeof(T) == 2) ? 4 : 0) k1_planar(K1Args a, PlanarGeom g) {
   constexpr int UB = PPT * C;                              // unit bytes
   constexpr int LW = (UB % 16 == 0) ? 16 : (UB % 8 == 0) ? 8 : 4;
   static_assert(UB % 4 == 0, "unit must be whole 32-bit words");
@@ -261,7 +290,9 @@ __global__ void __launch_bounds__(kThreads) k1_planar(K1Args a, PlanarGeom g) {
   // barrier) hides under the DRAM latency of those loads instead of preceding it: measured
   // 0.88 vs 0.83 of the HBM peak at batch 8 on four streams, 0.91 vs 0.82 for bf16 at 64 x 1024^2
   // (profiles/r1_k1_loads_first.txt).
-  asm volatile("griddepcontrol.launch_dependents;");
+  // (with statistics the dependent is the small fold kernel: it is released at the end instead, so that
+  // its CTA does not sit on an SM for the whole run)
+  if (!STATS) asm volatile("griddepcontrol.launch_dependents;");
   const bool loads_first = (a.flags & 1u) != 0;   // tuning: issue the first loads before the table build
   if (!loads_first) build_lut<T>(a, lut);
   asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -319,7 +350,10 @@ __global__ void __launch_bounds__(kThreads) k1_planar(K1Args a, PlanarGeom g) {
       }
     }
   }
-  if (STATS) finish_stats(a, acc);
+  if (STATS) {
+    asm volatile("griddepcontrol.launch_dependents;");
+    finish_stats(a, acc);
+  }
 }
 
 // ---- variant 3: bulk-async (TMA engine) staged input, planar output -----------------------------
@@ -567,6 +601,7 @@ __global__ void __launch_bounds__(kThreads) k1_pixel(K1Args a, PlanarGeom g) {
 }
 
 thread_local int g_last_variant = 0;
+thread_local int g_last_kernels = 0;
 
 int grid_for(uint64_t units_per_thread_total, int device_sms, int ctas_per_sm) {
   uint64_t need = (units_per_thread_total + kThreads - 1) / kThreads;
@@ -761,7 +796,51 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
   }
 }
 
-constexpr int kStatsMaxGrid = 148 * 8;
+// Scratch of the statistics reduction for a grid of at most `rows` CTAs: one row of partial sums per
+// CTA and, for grids that are folded in two steps, one row per kFoldRowsPerCta of them.  Nothing in it
+// has to be initialised: every row is written before the fold that reads it.
+struct StatsLayout {
+  uint64_t group_rows_off, bytes;
+};
+constexpr StatsLayout stats_layout(uint64_t rows) {
+  const uint64_t row = kMaxC * 2 * sizeof(double);
+  const uint64_t groups = (rows + kFoldRowsPerCta - 1) / kFoldRowsPerCta;
+  return StatsLayout{rows * row, (rows * row + groups * row + 255) / 256 * 256};
+}
+
+// Enqueue the fold of `n` rows behind the kernel that writes them.
+int launch_fold(const double* rows, double* group_rows, unsigned n, double* stats_out, unsigned cout, cudaStream_t st) {
+  auto launch = [&](unsigned grid, const double* in, unsigned count, unsigned per_cta, double* out, unsigned pairs) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kFoldThreads);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, k1_fold, in, count, per_cta, out, pairs);
+  };
+  if (n <= (unsigned)kFoldDirectMax) {
+    BT_CUDA_TRY(launch(1, rows, n, n, stats_out, cout));
+    g_last_kernels += 1;
+    return BT_OK;
+  }
+  const unsigned groups = (n + kFoldRowsPerCta - 1) / kFoldRowsPerCta;
+  BT_CUDA_TRY(launch(groups, rows, n, kFoldRowsPerCta, group_rows, kMaxC));
+  BT_CUDA_TRY(launch(1, group_rows, groups, groups, stats_out, cout));
+  g_last_kernels += 2;
+  return BT_OK;
+}
+
+// Caller-provided scratch covers the largest grid a launch can have (one pass per thread, capped at
+// kDefaultCtasPerSm CTAs per SM of a 148-SM part); the built-in array of
+// bt_preprocess_stats_static is smaller (see there).
+constexpr int kStatsMaxRows = 148 * kDefaultCtasPerSm;
+constexpr int kStaticRows = 148 * 8;
+
+int launch_checked(const bt_preprocess_params* p, void* stream, int stats_rows);
 
 }  // namespace
 
@@ -782,12 +861,20 @@ int bt_build_gamma_lut(double coeff, uint8_t lut[256]) {
 
 uint64_t bt_preprocess_scratch_bytes(const bt_preprocess_params* p) {
   if (!p || !p->stats_out) return 0;
-  return (uint64_t)kStatsMaxGrid * kMaxC * 2 * sizeof(double) + 256;
+  return stats_layout(kStatsMaxRows).bytes;
 }
 
 int bt_preprocess_last_variant(void) { return g_last_variant; }
+int bt_preprocess_last_kernels(void) { return g_last_kernels; }
 
-int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) {
+int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) { return launch_checked(p, stream, kStatsMaxRows); }
+
+}  // extern "C"
+
+namespace {
+
+// `stats_rows`: how many partial-sum rows `p->stats_scratch` has room for (bounds the grid).
+int launch_checked(const bt_preprocess_params* p, void* stream, int stats_rows) {
   if (!p || !p->src || !p->dst) return bt::fail(BT_E_INVALID, "bt_preprocess_launch: null pointer");
   if (p->batch < 0 || p->height < 0 || p->width < 0) return bt::fail(BT_E_INVALID, "negative extent");
   if (p->channels < 1 || p->channels > kMaxC) return bt::fail(BT_E_INVALID, "channels must be 1..4, got %d", p->channels);
@@ -821,24 +908,36 @@ int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) {
       if (a.stdev[c] == 0.0f) return bt::fail(BT_E_INVALID, "stdev[%d] is zero", c);
 
   const bool stats = p->stats_out != nullptr;
+  double* group_rows = nullptr;
   if (stats) {
-    a.partials = static_cast<double*>(p->stats_scratch);
-    a.ticket = reinterpret_cast<unsigned int*>(static_cast<uint8_t*>(p->stats_scratch) +
-                                               (uint64_t)kStatsMaxGrid * kMaxC * 2 * sizeof(double));
+    const StatsLayout lay = stats_layout((uint64_t)stats_rows);
+    uint8_t* base = static_cast<uint8_t*>(p->stats_scratch);
+    a.partials = reinterpret_cast<double*>(base);
+    group_rows = reinterpret_cast<double*>(base + lay.group_rows_off);
     a.stats_out = p->stats_out;
   }
   if ((uint64_t)a.B * a.H * a.W == 0) {
     if (stats) BT_CUDA_TRY(cudaMemsetAsync(p->stats_out, 0, sizeof(double) * 2 * a.Cout, st));
     g_last_variant = 0;
+    g_last_kernels = 0;
     return BT_OK;
   }
-  if (stats) {
-    // the arrival counter must start at zero; the kernel leaves it at zero, this covers first use
-    BT_CUDA_TRY(cudaMemsetAsync(a.ticket, 0, sizeof(unsigned int), st));
-  }
-
   int g = 0;
-  const int cap = stats ? kStatsMaxGrid : 0;
+  int cap = 0;
+  if (stats) {
+    // Every CTA of a statistics launch ends with a reduction (shuffles, a barrier, one row), so the
+    // grid that is best without statistics -- one pass per thread -- is not best with them.  Measured
+    // on B200 (profiles/r1_k1_stats_cap.txt): 16-bit and 8-bit outputs want one resident wave
+    // (4 CTAs per SM) looping over the batch, fp32 wants a single wave when the batch is small enough
+    // to need less than two, and 64 CTAs per SM otherwise.
+    cap = stats_rows;
+    if (((p->reserved >> 8) & 0xff) == 0) {
+      const int sms = sm_count();
+      const uint64_t ctas = ((uint64_t)a.B * a.H * a.W + 4095) / 4096;   // one pass: 16 pixels per thread
+      const int per_sm = (p->out_dtype != BT_F32 || ctas <= (uint64_t)sms * 8) ? 4 : 64;
+      if (sms * per_sm < cap) cap = sms * per_sm;
+    }
+  }
   switch (p->out_dtype) {
     case BT_F32:
       g = stats ? launch_typed<float, true>(p, a, p->variant, st, cap) : launch_typed<float, false>(p, a, p->variant, st, cap);
@@ -853,16 +952,21 @@ int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) {
   }
   if (g < 0) return g;
   BT_CUDA_TRY(cudaGetLastError());
+  g_last_kernels = 1;
+  if (stats) {
+    const int rc = launch_fold(a.partials, group_rows, (unsigned)g, p->stats_out, a.Cout, st);
+    if (rc != BT_OK) return rc;
+  }
   return BT_OK;
 }
 
-}  // extern "C"
+}  // namespace
 
 // ---------------------------------------------------------------------------------------------
 // bt_preprocess_stats_static: K1 with statistics for callers that must not allocate.
 //
 // The statistics reduction needs a little device memory besides the caller's input, output
-// and stats_out: one row of partial sums per CTA plus an arrival counter.  The regular entry
+// and stats_out: one row of partial sums per CTA (and two rows for a two-step fold).  The regular entry
 // point takes that memory from the caller (`stats_scratch`), which means somebody has to
 // cudaMalloc it.  Some users of this library cannot: a render or simulation plug-in that is
 // handed a fixed device-memory budget by its host application, a real-time ingest loop whose
@@ -878,8 +982,7 @@ int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) {
 #include <mutex>
 
 namespace {
-constexpr int kStaticRows = kStatsMaxGrid;                       // partial-sum rows in the static array
-constexpr uint64_t kStaticScratchBytes = (uint64_t)kStaticRows * kMaxC * 2 * sizeof(double) + 256;
+constexpr uint64_t kStaticScratchBytes = stats_layout(kStaticRows).bytes;   // 76 032: 1184 rows + 2 group rows, rounded to 256
 constexpr uint64_t kStaticBytesPerRow = 16384;                   // input bytes covered by one CTA's row
 constexpr uint64_t kStaticMaxInputBytes = (uint64_t)kStaticRows * kStaticBytesPerRow;  // 19 398 656
 constexpr int kMaxDevices = 64;
@@ -930,8 +1033,7 @@ extern "C" int bt_preprocess_stats_static(const bt_preprocess_params* p, void* s
   if (rc != BT_OK) return rc;
   bt_preprocess_params q = *p;
   q.stats_scratch = scratch;  // same kernel, same launch path; only the scratch differs
-  // bt_preprocess_launch zeroes the arrival counter (cudaMemsetAsync on `stream`) before every
-  // launch, so whatever an earlier call left in the shared array does not matter; the partial
-  // rows are fully overwritten by the CTAs that are launched before anything reads them.
-  return bt_preprocess_launch(&q, stream);
+  // Nothing in the array has to start at zero: whatever an earlier call left there does not matter,
+  // because every row a fold reads is written by this call's kernel first (stream order).
+  return launch_checked(&q, stream, kStaticRows);
 }

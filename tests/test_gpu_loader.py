@@ -56,7 +56,7 @@ def test_replay_with_fused_preprocess_equals_reference(golden_dir):
         np.testing.assert_array_equal(b["image_raw"].cpu().numpy(), exp["raw_b%d_image" % k])
         s, q = opre.batch_stats(want)
         np.testing.assert_allclose(b["image_stats"].cpu().numpy()[:, 0], s, rtol=1e-6, atol=1e-4)
-    assert dl.stats["kernels"] == 3
+    assert dl.stats["kernels"] == 6          # 3 batches x (K1 + the fold of its statistics rows)
 
 
 def test_shuffle_drop_last_and_item_transform(golden_dir):

@@ -93,6 +93,14 @@ def main():
         cases = [dict(shape=sh, dtype=dt, tune=t, streams=st) for sh in (C2, (16, 480, 640, 4), C4, C5)
                  for dt in (torch.float32, torch.bfloat16) for t in (0, 0x40000, 0x50000)
                  for st in ((1, 4) if sh[0] <= 16 else (1,))]
+    elif len(sys.argv) > 1 and sys.argv[1] == "stats":
+        cases = [dict(shape=sh, dtype=dt, stats=st, streams=n) for sh in (C2, C4, C3, C5)
+                 for dt in (torch.float32, torch.bfloat16) for st in (False, True)
+                 for n in ((1, 4) if sh == C2 else (1,))]
+    elif len(sys.argv) > 1 and sys.argv[1] == "statscap":
+        cases = [dict(shape=sh, dtype=dt, stats=True, streams=n, tune=cap << 8) for sh in (C2, C4, C5)
+                 for dt in (torch.float32, torch.bfloat16) for cap in (0, 4, 8, 16, 32, 64)
+                 for n in ((1, 4) if sh == C2 else (1,))]
     elif len(sys.argv) > 1 and sys.argv[1] == "bulk":
         cases = []
         for shape in (C2, C4, C3, C5):
