@@ -675,6 +675,15 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
   auto grid_of = [&](uint64_t units, int unroll) {
     int g = grid_for((units + unroll - 1) / unroll, sms, tune_ctas ? tune_ctas : kDefaultCtasPerSm);
     if (grid_cap > 0 && g > grid_cap) g = grid_cap;
+    if (!tune_ctas && !STATS) {
+      // One resident wave is 4 CTAs per SM for these kernels.  A grid that exceeds it by a few CTAs
+      // (the headline 8 x 640 x 480 batch: 600 CTAs on 592 slots) would run a second, nearly empty
+      // wave: let a few threads take a second unit instead (11.7 -> 10.3 us for an isolated launch).
+      // 16-bit outputs move fewer bytes per CTA and prefer the single looping wave up to the size
+      // where the 4-unit kernel takes over (profiles/r1_k1_wave.txt).
+      const int wave = sms * 4;
+      if (g > wave && (g <= wave + wave / 10 || (sizeof(T) == 2 && units < (1u << 20)))) g = wave;
+    }
     return g;
   };
 #define LAUNCH_PLANAR(C_, PPT_, UNR_)                                                       \

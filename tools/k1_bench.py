@@ -101,6 +101,9 @@ def main():
         cases = [dict(shape=sh, dtype=dt, stats=True, streams=n, tune=cap << 8) for sh in (C2, C4, C5)
                  for dt in (torch.float32, torch.bfloat16) for cap in (0, 4, 8, 16, 32, 64)
                  for n in ((1, 4) if sh == C2 else (1,))]
+    elif len(sys.argv) > 1 and sys.argv[1] == "wave":
+        cases = [dict(shape=(b, 480, 640, 4), dtype=dt, streams=n, tune=cap << 8) for b in (8, 12, 16, 24)
+                 for dt in (torch.float32, torch.bfloat16) for cap in (0, 3, 4, 8) for n in (1, 4)]
     elif len(sys.argv) > 1 and sys.argv[1] == "bulk":
         cases = []
         for shape in (C2, C4, C3, C5):
