@@ -70,12 +70,22 @@ template <> struct OutT<uint8_t> {
 // Build the per-channel value table with the reference's expression.
 template <typename T>
 __device__ __forceinline__ void build_lut(const K1Args& a, T* lut /* [kMaxC][256] */) {
-  for (uint32_t i = threadIdx.x; i < kMaxC * 256; i += blockDim.x) {
-    uint32_t c = i >> 8, v = i & 255;
-    uint8_t g = (a.use_gamma && c < 3) ? a.gamma_lut[v] : (uint8_t)v;
-    float o = (float)g;
+  static_assert(kThreads == 256, "one thread per table index");
+  // Thread v makes entry v of every channel.  The gamma byte is read once, as the 32-bit word that
+  // holds it (a warp touches 8 distinct words of the parameter bank instead of 32 distinct bytes),
+  // and the channel loop is unrolled so that mean/stdev are plain constant operands.
+  const uint32_t v = threadIdx.x;
+  uint32_t g = v;
+  if (a.use_gamma) {
+    const uint32_t word = reinterpret_cast<const uint32_t*>(a.gamma_lut)[v >> 2];
+    g = (word >> (8 * (v & 3))) & 0xffu;
+  }
+#pragma unroll
+  for (int c = 0; c < kMaxC; ++c) {
+    const uint32_t gc = c < 3 ? g : v;   // alpha is never gamma-corrected (offscreen.py:109-111)
+    float o = (float)gc;
     if (a.use_norm) o = __fdiv_rn(__fsub_rn(o, a.mean[c]), a.stdev[c]);
-    lut[i] = OutT<T>::make(o, g);
+    lut[c * 256 + v] = OutT<T>::make(o, (uint8_t)gc);
   }
   __syncthreads();
 }
@@ -664,6 +674,18 @@ void launch_planar(K kernel, int grid, cudaStream_t st, const K1Args& a, const G
   cudaLaunchKernelEx(&cfg, kernel, a, geo);
 }
 
+// CTAs of `kernel` that fit on one SM (asked once per kernel).
+template <auto Kernel>
+int resident_ctas() {
+  static int cached = 0;   // one instance per kernel; a race writes the same value twice
+  if (cached == 0) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, Kernel, kThreads, 0) != cudaSuccess || n < 1) n = 4;
+    cached = n;
+  }
+  return cached;
+}
+
 template <typename T, bool STATS>
 int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStream_t st, int grid_cap) {
   const int sms = sm_count();
@@ -672,16 +694,16 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
   const bool aligned_dst = reinterpret_cast<uintptr_t>(a.dst) % 16 == 0;
   const bool can_vec = aligned_src && aligned_dst && variant != 1;
   const int tune_ctas = (p->reserved >> 8) & 0xff;
-  auto grid_of = [&](uint64_t units, int unroll) {
+  auto grid_of = [&](uint64_t units, int unroll, int resident = 0) {
     int g = grid_for((units + unroll - 1) / unroll, sms, tune_ctas ? tune_ctas : kDefaultCtasPerSm);
     if (grid_cap > 0 && g > grid_cap) g = grid_cap;
-    if (!tune_ctas && !STATS) {
-      // One resident wave is 4 CTAs per SM for these kernels.  A grid that exceeds it by a few CTAs
-      // (the headline 8 x 640 x 480 batch: 600 CTAs on 592 slots) would run a second, nearly empty
-      // wave: let a few threads take a second unit instead (11.7 -> 10.3 us for an isolated launch).
-      // 16-bit outputs move fewer bytes per CTA and prefer the single looping wave up to the size
-      // where the 4-unit kernel takes over (profiles/r1_k1_wave.txt).
-      const int wave = sms * 4;
+    if (!tune_ctas && !STATS && resident > 0) {
+      // `resident` CTAs per SM make one wave.  A grid that exceeds it by a few CTAs would run a
+      // second, nearly empty wave: let a few threads take a second unit instead (an isolated batch-8
+      // launch of 600 CTAs on 592 slots: 11.7 -> 10.3 us).  16-bit outputs move fewer bytes per
+      // CTA and prefer the single looping wave up to the size where the 4-unit kernel takes over
+      // (profiles/r1_k1_wave.txt).
+      const int wave = sms * resident;
       if (g > wave && (g <= wave + wave / 10 || (sizeof(T) == 2 && units < (1u << 20)))) g = wave;
     }
     return g;
@@ -690,7 +712,7 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
   do {                                                                                      \
     PlanarGeom geo;                                                                         \
     if (!planar_geom(a, (PPT_), geo)) break; /* too many units for 32-bit indices */        \
-    int g = grid_of(geo.total_units, (UNR_));                                               \
+    int g = grid_of(geo.total_units, (UNR_), resident_ctas<k1_planar<T, C_, PPT_, UNR_, STATS>>()); \
     launch_planar(k1_planar<T, C_, PPT_, UNR_, STATS>, g, st, a, geo, !((p->reserved >> 16) & 1)); \
     g_last_variant = 2;                                                                     \
     return g;                                                                               \
