@@ -104,6 +104,14 @@ def main():
     elif len(sys.argv) > 1 and sys.argv[1] == "wave":
         cases = [dict(shape=(b, 480, 640, 4), dtype=dt, streams=n, tune=cap << 8) for b in (8, 12, 16, 24)
                  for dt in (torch.float32, torch.bfloat16) for cap in (0, 3, 4, 8) for n in (1, 4)]
+    elif len(sys.argv) > 1 and sys.argv[1] == "retune":
+        cases = [dict(shape=C2, dtype=torch.float32, streams=n, tune=t) for n in (1, 2, 3, 4, 8)
+                 for t in (0, 0x40000, 2, 8, 1)]
+        cases += [dict(shape=sh, dtype=torch.float32, tune=t) for sh in (C4, C5) for t in (0, 0x40000, 2, 8)]
+        cases += [dict(shape=sh, dtype=torch.bfloat16, tune=t, streams=n) for sh in (C2, C4) for t in (0, 0x40000, 4, 1)
+                  for n in ((1, 2, 4) if sh == C2 else (1,))]
+        cases += [dict(shape=C2, dtype=torch.float32, variant=v, streams=n) for v in ("bulk",) for n in (1, 2, 4)]
+        cases += [dict(shape=C4, dtype=torch.float32, variant="bulk")]
     elif len(sys.argv) > 1 and sys.argv[1] == "bulk":
         cases = []
         for shape in (C2, C4, C3, C5):
