@@ -351,7 +351,10 @@ __global__ void __launch_bounds__(kThreads, (STATS || sizeof(T) == 2) ? 4 : 0) k
           float fs = 0.f, fq = 0.f;
 #pragma unroll
           for (int p = 0; p < PPT; ++p) {
-            vals[p] = lut[c * 256 + byte_of(words, p * C + c)];
+            const uint32_t v = byte_of(words, p * C + c);
+            // uint8 output has no normalisation and gamma leaves alpha alone: channel 3 passes through
+            if (sizeof(T) == 1 && c == 3) vals[p] = OutT<T>::make((float)v, (uint8_t)v);
+            else vals[p] = lut[c * 256 + v];
             if (STATS) { float f = OutT<T>::as_float(vals[p]); fs += f; fq = fmaf(f, f, fq); }
           }
           st_stream<T, PPT>(dst + out_off[j] + (uint64_t)c * plane, vals);
@@ -780,7 +783,9 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
           k1_interleaved<T, 4, STATS, true, 0><<<g, kThreads, 0, st>>>(a, geo);
         else if (a.C == 4)
           k1_interleaved<T, 4, STATS, false, 4><<<g, kThreads, 0, st>>>(a, geo);
-        else if (a.C == 1)
+        else if (a.C == 1 || (sizeof(T) == 1 && !STATS))
+          // one table serves every byte: a single channel, or uint8 output of 2-3 colour channels
+          // (no normalisation, and gamma treats channels 0..2 alike)
           k1_interleaved<T, 4, STATS, false, 1><<<g, kThreads, 0, st>>>(a, geo);
         else
           k1_interleaved<T, 4, STATS, false, 0><<<g, kThreads, 0, st>>>(a, geo);
