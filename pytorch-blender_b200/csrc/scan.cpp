@@ -531,6 +531,26 @@ int stream_big_target(const bt_schema* schema, int* column) {
   const Scanner& s = tls_scanner();
   if (s.marks.empty()) return BT_E_UNSUPPORTED;
   const int m = s.marks.back();
+  if (m >= 2 && (int)s.stack.size() - m == 1) {
+    // Protocol 5:  ... key, GLOBAL numpy._core.numeric._frombuffer, MARK, <external bytes>  -- the
+    // buffer is the first argument, dtype and shape follow it on the wire.  The key and the byte
+    // count pick the column now; place_fields checks dtype and shape once they are known, and a
+    // mismatch sends the message through the caller's decode with its bytes put back together.
+    const Node& fn = s.nodes[s.stack[m - 1]];
+    const Node& key = s.nodes[s.stack[m - 2]];
+    if (key.k != N_STR || key.len >= BT_MAX_KEY ||
+        !global_is(s, fn, "numpy.core.numeric", "numpy._core.numeric", "_frombuffer"))
+      return BT_E_UNSUPPORTED;
+    for (size_t ci = 0; ci < schema->cols.size(); ++ci) {
+      const bt_column& c = schema->cols[ci];
+      if (strlen(c.key) != key.len || memcmp(c.key, s.p + key.off, key.len) != 0) continue;
+      if (c.kind != BT_KIND_NDARRAY || c.item_bytes != s.big_len) return BT_E_SCHEMA;
+      *column = (int)ci;
+      g_ext_cols.push_back((int)ci);
+      return BT_OK;
+    }
+    return BT_E_SCHEMA;
+  }
   if (m < 2 || (int)s.stack.size() - m != 5) return BT_E_UNSUPPORTED;
   const Node& owner = s.nodes[s.stack[m - 1]];
   const Node& key = s.nodes[s.stack[m - 2]];

@@ -26,6 +26,7 @@
 #include <unistd.h>
 
 #include <cerrno>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -56,7 +57,15 @@ struct Peer {
   enum State { IDLE, CONNECTING, READY } state = IDLE;
   uint64_t retry_at = 0;
   uint32_t backoff_ms = 20;
+  // Read-ahead: every socket read asks for as much as fits here, so the frame header, the pickle
+  // prologue and the few bytes after a payload (plus the next message's header) cost one recv()
+  // instead of one each.  Only what is not array payload passes through it: payload bytes beyond
+  // what a read-ahead happened to bring along are still received straight into the staging slot.
+  std::vector<uint8_t> ahead;
+  size_t rpos = 0, wpos = 0;
 };
+
+constexpr size_t kAheadBytes = 8192 + 64;
 
 struct External {
   uint64_t compact_pos;
@@ -69,6 +78,7 @@ constexpr int kIoTimeoutMs = 10000;  // a message that started arriving must com
 void close_peer(Peer& p) {
   if (p.fd >= 0) close(p.fd);
   p.fd = -1;
+  p.rpos = p.wpos = 0;   // bytes of a broken connection are not the start of anything
   p.state = Peer::IDLE;
   p.retry_at = now_ms() + p.backoff_ms;
   if (p.backoff_ms < 500) p.backoff_ms *= 2;
@@ -102,6 +112,81 @@ int write_all(int fd, const uint8_t* src, size_t n, int timeout_ms) {
     if (now >= deadline) return bt::fail(BT_E_IO, "peer does not accept the handshake");
     pollfd pf = {fd, POLLOUT, 0};
     poll(&pf, 1, (int)(deadline - now));
+  }
+  return BT_OK;
+}
+
+inline size_t ahead_avail(const Peer& p) { return p.wpos - p.rpos; }
+
+// Diagnostic switch (A/B measurements): BT_RX_READAHEAD=0 makes every read ask for exactly the bytes
+// it needs, as the first version of this endpoint did.
+bool readahead_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("BT_RX_READAHEAD");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
+// One non-blocking recv() into the free part of the read-ahead buffer.
+// > 0: bytes read, 0: nothing there right now, < 0: the connection is unusable.
+int fill_once(Peer& p) {
+  if (p.ahead.size() != kAheadBytes) p.ahead.resize(kAheadBytes);
+  if (p.rpos == p.wpos) p.rpos = p.wpos = 0;
+  if (p.wpos == kAheadBytes) {
+    if (p.rpos == 0) return 0;   // full
+    memmove(p.ahead.data(), p.ahead.data() + p.rpos, p.wpos - p.rpos);
+    p.wpos -= p.rpos;
+    p.rpos = 0;
+  }
+  while (true) {
+    ssize_t k = recv(p.fd, p.ahead.data() + p.wpos, kAheadBytes - p.wpos, 0);
+    if (k > 0) { p.wpos += (size_t)k; return (int)k; }
+    if (k == 0) return bt::fail(BT_E_IO, "peer closed the connection");
+    if (errno == EINTR) continue;
+    if (errno == EAGAIN || errno == EWOULDBLOCK) return 0;
+    return bt::fail(BT_E_IO, "recv: %s", strerror(errno));
+  }
+}
+
+// Make at least n (<= 64) bytes available in the read-ahead buffer.
+int need(Peer& p, size_t n, int timeout_ms) {
+  const uint64_t deadline = now_ms() + (uint64_t)timeout_ms;
+  while (ahead_avail(p) < n) {
+    if (p.wpos == kAheadBytes && p.rpos > 0) {   // make room at the end
+      memmove(p.ahead.data(), p.ahead.data() + p.rpos, p.wpos - p.rpos);
+      p.wpos -= p.rpos;
+      p.rpos = 0;
+    }
+    const int k = fill_once(p);
+    if (k < 0) return k;
+    if (k > 0) continue;
+    const uint64_t now = now_ms();
+    if (now >= deadline) return bt::fail(BT_E_IO, "peer stalled in the middle of a message");
+    pollfd pf = {p.fd, POLLIN, 0};
+    poll(&pf, 1, (int)(deadline - now));
+  }
+  return BT_OK;
+}
+
+// n bytes of the stream to dst.  Small requests (headers, pickle prologue, the bytes after a payload)
+// go through the read-ahead buffer: when it is empty the socket is asked for a buffer-full, because
+// whatever follows is needed next anyway.  Large requests (array payloads) take what the buffer
+// happens to hold and recv() the rest straight into dst.
+int take(Peer& p, uint8_t* dst, uint64_t n, int timeout_ms, bool small) {
+  while (n) {
+    size_t have = ahead_avail(p);
+    if (have == 0) {
+      if (!small || !readahead_enabled()) return read_exact(p.fd, dst, n, timeout_ms);
+      int rc = need(p, 1, timeout_ms);
+      if (rc != BT_OK) return rc;
+      have = ahead_avail(p);
+    }
+    const size_t k = have < n ? have : (size_t)n;
+    memcpy(dst, p.ahead.data() + p.rpos, k);
+    p.rpos += k;
+    dst += k;
+    n -= k;
   }
   return BT_OK;
 }
@@ -225,6 +310,27 @@ void finish_connect(Peer& p) {
 // Drive the connections; return the index of a READY peer with bytes to read, or -1 after timeout_ms.
 int wait_readable(bt_pull* q, int timeout_ms) {
   const uint64_t deadline = now_ms() + (uint64_t)(timeout_ms < 0 ? 0 : timeout_ms);
+  const size_t npeers = q->peers.size();
+  // Fast path while every connection is up: the peer whose turn it is usually has bytes waiting --
+  // read ahead earlier, or in its socket, which one speculative recv() finds out more cheaply than
+  // a poll() over all peers.  Turn order is kept, so fair queuing is too.
+  bool all_ready = npeers > 0;
+  for (const Peer& p : q->peers) all_ready = all_ready && p.state == Peer::READY;
+  if (all_ready && readahead_enabled()) {
+    int tries = 0;
+    for (size_t k = 0; k < npeers && tries < 2; ++k) {
+      const size_t i = (q->rr + k) % npeers;
+      Peer& p = q->peers[i];
+      if (ahead_avail(p) == 0) {
+        ++tries;
+        const int got = fill_once(p);
+        if (got < 0) { close_peer(p); break; }
+        if (got == 0) continue;
+      }
+      q->rr = (i + 1) % npeers;
+      return (int)i;
+    }
+  }
   while (true) {
     const uint64_t now = now_ms();
     q->pfds.clear();
@@ -238,6 +344,8 @@ int wait_readable(bt_pull* q, int timeout_ms) {
       q->pfds.push_back(pf);
     }
     int wait = now >= deadline ? 0 : (int)(deadline - now);
+    for (const Peer& p : q->peers)
+      if (p.state == Peer::READY && ahead_avail(p) > 0) wait = 0;   // something is readable already
     if (next_retry != ~0ull) {
       const int until = next_retry > now ? (int)(next_retry - now) : 0;
       if (until < wait) wait = until;
@@ -252,7 +360,7 @@ int wait_readable(bt_pull* q, int timeout_ms) {
       const size_t i = (q->rr + k) % n;
       Peer& p = q->peers[i];
       if (p.state != Peer::READY) continue;
-      if (q->pfds[i].revents & POLLIN) {
+      if ((q->pfds[i].revents & POLLIN) || ahead_avail(p) > 0) {
         q->rr = (i + 1) % n;
         return (int)i;
       }
@@ -265,11 +373,11 @@ int wait_readable(bt_pull* q, int timeout_ms) {
 // Read one frame header.  *is_msg = 0 for a command (skipped), 1 for a message of `*size` bytes.
 int read_frame_header(Peer& p, int* is_msg, uint64_t* size) {
   uint8_t h[9];
-  int rc = read_exact(p.fd, h, 2, kIoTimeoutMs);
+  int rc = take(p, h, 2, kIoTimeoutMs, true);
   if (rc != BT_OK) return rc;
   uint64_t sz = h[1];
   if (h[0] & 0x02) {
-    rc = read_exact(p.fd, h + 2, 7, kIoTimeoutMs);
+    rc = take(p, h + 2, 7, kIoTimeoutMs, true);
     if (rc != BT_OK) return rc;
     sz = 0;
     for (int i = 1; i < 9; ++i) sz = (sz << 8) | h[i];
@@ -279,7 +387,7 @@ int read_frame_header(Peer& p, int* is_msg, uint64_t* size) {
     uint64_t left = sz;
     while (left) {
       const uint64_t k = left < skip.size() ? left : skip.size();
-      rc = read_exact(p.fd, skip.data(), k, kIoTimeoutMs);
+      rc = take(p, skip.data(), k, kIoTimeoutMs, true);
       if (rc != BT_OK) return rc;
       left -= k;
     }
@@ -296,7 +404,7 @@ int read_frame_header(Peer& p, int* is_msg, uint64_t* size) {
 // Whole message into q->held.
 int read_whole(bt_pull* q, Peer& p, uint64_t size) {
   q->held.resize(size);
-  int rc = read_exact(p.fd, q->held.data(), size, kIoTimeoutMs);
+  int rc = take(p, q->held.data(), size, kIoTimeoutMs, size <= kAheadBytes);
   if (rc != BT_OK) return rc;
   q->has_held = true;
   return BT_OK;
@@ -318,7 +426,7 @@ int rebuild_into_held(bt_pull* q, Peer& p, uint64_t msg_size, uint64_t consumed)
   const uint64_t have = out.size();
   if (have != consumed) return bt::fail(BT_E_IO, "internal: streamed byte count mismatch");
   out.resize(msg_size);
-  int rc = read_exact(p.fd, out.data() + have, msg_size - have, kIoTimeoutMs);
+  int rc = take(p, out.data() + have, msg_size - have, kIoTimeoutMs, msg_size - have <= kAheadBytes);
   if (rc != BT_OK) return rc;
   q->has_held = true;
   return BT_OK;
@@ -341,7 +449,7 @@ int receive_streaming(bt_pull* q, Peer& p, uint64_t msg_size, bt_ring* ring, int
     if (want == 0) { why = BT_E_UNSUPPORTED; break; }  // the pickle wants more bytes than the frame has
     const size_t old = q->cb.size();
     q->cb.resize(old + want);
-    int rc = read_exact(p.fd, q->cb.data() + old, want, kIoTimeoutMs);
+    int rc = take(p, q->cb.data() + old, want, kIoTimeoutMs, true);
     if (rc != BT_OK) return rc;
     consumed += want;
     // run the scanner over what is buffered; it may stop on several large payloads in a row
@@ -364,7 +472,7 @@ int receive_streaming(bt_pull* q, Peer& p, uint64_t msg_size, bt_ring* ring, int
       uint8_t* dst = base + c.slot_off + c.item_bytes * (uint64_t)item;
       memcpy(dst, q->cb.data() + pos, have);
       q->cb.resize(pos);
-      rc = read_exact(p.fd, dst + have, len - have, kIoTimeoutMs);
+      rc = take(p, dst + have, len - have, kIoTimeoutMs, false);
       if (rc != BT_OK) return rc;
       consumed += len - have;
       q->ext.push_back(External{pos, len, dst});
@@ -373,7 +481,7 @@ int receive_streaming(bt_pull* q, Peer& p, uint64_t msg_size, bt_ring* ring, int
   if (why == BT_OK) {
     if (consumed < msg_size) {  // bytes after the pickle's STOP: not ours to interpret
       std::vector<uint8_t> tail(msg_size - consumed);
-      int rc = read_exact(p.fd, tail.data(), tail.size(), kIoTimeoutMs);
+      int rc = take(p, tail.data(), tail.size(), kIoTimeoutMs, tail.size() <= kAheadBytes);
       if (rc != BT_OK) return rc;
       q->cb.insert(q->cb.end(), tail.begin(), tail.end());
       consumed = msg_size;

@@ -97,7 +97,11 @@ def test_streams_from_an_unmodified_push_socket(protocol, extra):
     while not rx.recv(200):
         assert time.time() < deadline
     sch = Schema.from_message(rx.pending(), 3)
-    got = _drain(rx, sch, 7, 3)
+
+    def no_fallback(obj):
+        pytest.fail("protocol %d message left the streaming path: %s" % (protocol, N.last_error()))
+
+    got = _drain(rx, sch, 7, 3, on_odd=no_fallback)
     t.join()
     rx.close()
     exp = default_collate(msgs)
@@ -185,3 +189,48 @@ def test_publisher_restart_is_picked_up_again():
     ids = [(int(b["btid"][i]), int(b["frameid"][i])) for b in got for i in range(len(b["frameid"]))]
     assert ids == [(4, 0), (4, 1), (4, 2), (5, 0), (5, 1), (5, 2), (5, 3)]
     np.testing.assert_array_equal(got[1]["image"][3], second[3]["image"])
+
+
+@pytest.mark.parametrize("shape", [(8, 8, 4), (45, 47, 4), (90, 91, 4), (128, 128, 4)])
+def test_read_ahead_keeps_every_byte_in_place(shape):
+    """Frames from far below to far above the endpoint's read-ahead buffer (8 KiB): several messages
+    per socket read, messages that straddle a read, payloads that start in the buffer and finish in the
+    slot, an odd message in the middle of a burst, three publishers served in turn.  Every message
+    arrives once, bit for bit."""
+    per_pub, pubs, B = 40, 3, 16
+    addrs = [_free_tcp() for _ in range(pubs)]
+    all_msgs, threads = {}, []
+    for k, addr in enumerate(addrs):
+        ms = _msgs(per_pub, shape=shape, seed=10 + k)
+        blobs = [pickle.dumps(m, protocol=3 + (k % 3)) for m in ms]
+        if k == 1:   # a message outside the schema in the middle of the stream
+            blobs[17] = pickle.dumps(dict(ms[17], image=ms[17]["image"][:-1]), protocol=3)
+        for m in ms:
+            all_msgs[(10 + k, m["frameid"])] = m
+        threads.append(_publisher(addr, blobs, delay=0.2 * k))
+    rx = DirectReceiver(addrs)
+    deadline = time.time() + 20
+    while not rx.recv(200):
+        assert time.time() < deadline
+    sch = Schema.from_message(rx.pending(), B)
+    odd = []
+
+    def fix(obj):
+        odd.append(obj["image"].shape)
+        obj["image"] = all_msgs[(obj["btid"], obj["frameid"])]["image"]
+        return obj
+
+    got = _drain(rx, sch, per_pub * pubs, B, on_odd=fix)
+    for t in threads:
+        t.join()
+    rx.close()
+    assert odd == [(shape[0] - 1,) + shape[1:]]
+    seen = set()
+    for b in got:
+        for i in range(len(b["frameid"])):
+            key = (int(b["btid"][i]), int(b["frameid"][i]))
+            assert key not in seen
+            seen.add(key)
+            np.testing.assert_array_equal(b["image"][i], all_msgs[key]["image"])
+            np.testing.assert_array_equal(b["bbox"][i], all_msgs[key]["bbox"])
+    assert len(seen) == per_pub * pubs
