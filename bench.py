@@ -308,10 +308,12 @@ def large_batch_probe(torch, btt, dev, spec):
     return B2 * H2 * W2 * C * 5 / sec / 1e9, sec
 
 
-def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_threads=1, shm_slots=0, rx="auto"):
+def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_threads=1, shm_slots=0, rx="auto",
+            raw_parts=False):
     """Public API with host buffers: publishers -> DeviceLoader -> device batch (+ stats read back)."""
     addrs, procs = spawn_publishers("blendtorch.btt.synthetic", PUBLISHERS, transport, tag="r%s" % os.environ.get("RANK", "0"),
-                                    extra=("--shm-slots", str(shm_slots)) if shm_slots else ())
+                                    extra=(("--shm-slots", str(shm_slots)) if shm_slots else ()) +
+                                          (("--raw-parts",) if raw_parts else ()))
     try:
         total = (steps + warmup) * BATCH
         per_recv = -(-(steps + warmup) // receivers) * BATCH

@@ -64,9 +64,13 @@ typedef enum bt_kind {
   BT_KIND_NONE = 4,
   BT_KIND_STR = 5,     /* UTF-8 span in the message */
   BT_KIND_OTHER = 6,   /* parsed but not representable as a column */
-  BT_KIND_SHMREF = 7   /* ndarray announced by reference into a shared-memory segment (bt_shm_*):
+  BT_KIND_SHMREF = 7,  /* ndarray announced by reference into a shared-memory segment (bt_shm_*):
                           dtype/ndim/shape describe it, payload_off/len span the segment NAME inside
                           the message, ival is the slot index */
+  BT_KIND_RAWREF = 8   /* ndarray whose bytes travel as a separate frame of the same multipart message
+                          (raw-parts wire, DataPublisher(raw_parts=True)): dtype/ndim/shape describe it,
+                          ival is the 1-based index of the frame; payload_off/len are 0 until the
+                          receiver has the frame (then they say where its bytes are) */
 } bt_kind;
 
 #define BT_MAX_DIMS 8
@@ -229,6 +233,12 @@ int bt_pull_connect(bt_pull* q, const char* address);   /* "tcp://host:port" or 
 int bt_pull_destroy(bt_pull* q);
 int bt_pull_recv(bt_pull* q, int timeout_ms);            /* hold one whole message (BT_OK) or BT_E_TIMEOUT */
 int bt_pull_pending(bt_pull* q, const uint8_t** data, uint64_t* len);
+/* Frames of the held message: returns their number and writes up to max_parts sizes.  1 for the
+ * reference wire.  More for the opt-in raw-parts wire (no reference counterpart; publisher.py:43 sends
+ * one pickled frame): frame 0 is the pickled dict in which every large array is the tuple
+ * ("__btraw__", k, dtype_str, shape) and frame k holds that array's bytes; bt_pull_pending then spans
+ * all frames back to back.  bt_pull_fill receives such frames straight into their schema columns. */
+int bt_pull_pending_parts(bt_pull* q, uint64_t* sizes, int max_parts);
 int bt_pull_drop(bt_pull* q);
 int bt_pull_fill(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, int first_item, int max_items,
                  int slice_ms, int* n_done);

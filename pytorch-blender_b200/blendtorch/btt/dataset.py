@@ -18,6 +18,7 @@ import zmq
 
 from .constants import DEFAULT_TIMEOUTMS
 from . import shm
+from . import wire
 from .file import FileReader, FileRecorder
 
 
@@ -94,10 +95,15 @@ class RemoteIterableDataset(tud.IterableDataset):
                     ready = dict(poller.poll(self.timeoutms))
                     assert sock in ready, "No response within timeout interval."
                     data = sock.recv()
-                    obj = shm.resolve(pickle.loads(data))
+                    if sock.getsockopt(zmq.RCVMORE):
+                        # raw-parts wire (wire.py): the arrays follow as frames of their own
+                        obj = shm.resolve(wire.decode([data] + sock.recv_multipart(copy=False)))
+                        data = None
+                    else:
+                        obj = shm.resolve(pickle.loads(data))
                     if rec is not None:
-                        if shm.MARKER_BYTES in data[:4096]:
-                            # shared-memory wire: record the message with its payload in-line
+                        if data is None or shm.MARKER_BYTES in data[:4096]:
+                            # opt-in wires: record the message with its payload in-line
                             data = pickle.dumps(obj, protocol=3)
                         rec.save(data, is_pickled=True)
                     yield self._item(obj)

@@ -35,6 +35,7 @@ import zmq
 
 from . import native as N
 from . import shm
+from . import wire
 from .dataset import FileDataset, RemoteIterableDataset, open_pull_socket
 from .file import FileRecorder
 from .preprocess import PreparedPreprocess, Preprocess
@@ -283,11 +284,11 @@ class DeviceLoader:
         return n // self.batch_size if self.drop_last else -(-n // self.batch_size)
 
     # ---- producers --------------------------------------------------------------------------
-    def _new_stager(self, first_msg, rid=0):
+    def _new_stager(self, first_msg, rid=0, sizes=None):
         """Stager for the stream that starts with `first_msg`.  Pinned rings are expensive to create
         (page-locking hundreds of MB takes longer than an epoch of small recordings), so a stager
         is kept per producer and reused by later epochs while the layout stays the same."""
-        schema = Schema.from_message(first_msg, self.batch_size)
+        schema = Schema.from_message(first_msg, self.batch_size, sizes)
         for key in self.specs:
             c = schema.column(key)  # KeyError: the named image field is not in the messages
             if c.dtype != np.uint8:
@@ -414,6 +415,19 @@ class DeviceLoader:
             self._retire(stager)
             out_q.put(_DONE)
 
+    @staticmethod
+    def _decode_pending(rx):
+        """The held message as the object the producer published (the reference's decode, for either
+        framing): raw-parts frames are joined, shared-memory references fetched."""
+        msg, sizes = rx.pending(), rx.pending_parts()
+        if len(sizes) > 1:
+            obj = wire.loads(msg, sizes)
+        elif rx.more():
+            obj = wire.decode([bytes(msg)] + rx.recv_rest())
+        else:
+            obj = pickle.loads(msg)
+        return shm.resolve(obj)
+
     def _stream_fast(self, ds, rx, out_q, stop, holder):
         """Batches filled by a C receive loop (`Receiver`: libzmq socket, `DirectReceiver`: own ZMTP
         endpoint): one call per batch, no GIL per message."""
@@ -428,7 +442,7 @@ class DeviceLoader:
                 assert waited < ds.timeoutms, "No response within timeout interval."
             if remaining <= 0:
                 return
-            stager = self._new_stager(rx.pending(), self._rid())
+            stager = self._new_stager(rx.pending(), self._rid(), rx.pending_parts())
             holder.append(stager)
             ring, schema = stager.ring, stager.schema
             while remaining > 0 and not stop.is_set():
@@ -456,7 +470,7 @@ class DeviceLoader:
                         assert waited < ds.timeoutms, "No response within timeout interval."
                         continue
                     # this message is outside the native subset: the reference's own decode, same slot
-                    stager.schema.ingest_object(ring.view(slot), filled, shm.resolve(pickle.loads(rx.pending())), host_rows)
+                    stager.schema.ingest_object(ring.view(slot), filled, self._decode_pending(rx), host_rows)
                     rx.drop()
                     self.stats["compat_items"] += 1
                     filled += 1
@@ -495,13 +509,14 @@ class DeviceLoader:
                 assert waited < ds.timeoutms, "No response within timeout interval."
             frame = sock.recv(copy=False)
             msg = frame.buffer
+            parts = sock.recv_multipart(copy=False) if sock.getsockopt(zmq.RCVMORE) else None   # raw-parts wire
             if stager is not None:
                 stager.ring.reap()
-            by_ref = shm.MARKER_BYTES in bytes(msg[:4096]) if (rec is not None or custom) else False
+            by_ref = parts is not None or (shm.MARKER_BYTES in bytes(msg[:4096]) if (rec is not None or custom) else False)
             if rec is not None and not by_ref:
                 rec.save(msg, is_pickled=True)
-            if custom or (rec is not None and by_ref):
-                obj = shm.resolve(pickle.loads(msg))
+            if custom or parts is not None or (rec is not None and by_ref):
+                obj = shm.resolve(wire.decode([msg] + parts) if parts is not None else pickle.loads(msg))
                 if rec is not None and by_ref:
                     # recordings must be self-contained: store the message with its payload in-line
                     rec.save(pickle.dumps(obj, protocol=3), is_pickled=True)

@@ -17,7 +17,7 @@ BT_E_CUDA, BT_E_NOMEM, BT_E_IO, BT_E_TIMEOUT, BT_E_TOO_LARGE = -5, -6, -7, -8, -
 (BT_U8, BT_I8, BT_U16, BT_I16, BT_U32, BT_I32, BT_U64, BT_I64,
  BT_F16, BT_F32, BT_F64, BT_BOOL, BT_BF16) = range(13)
 (BT_KIND_NDARRAY, BT_KIND_INT, BT_KIND_FLOAT, BT_KIND_BOOL,
- BT_KIND_NONE, BT_KIND_STR, BT_KIND_OTHER, BT_KIND_SHMREF) = range(8)
+ BT_KIND_NONE, BT_KIND_STR, BT_KIND_OTHER, BT_KIND_SHMREF, BT_KIND_RAWREF) = range(9)
 
 BT_MAX_DIMS = 8
 BT_MAX_KEY = 64
@@ -114,6 +114,7 @@ def _load():
         "bt_pull_destroy": (i32, [vp]),
         "bt_pull_recv": (i32, [vp, i32]),
         "bt_pull_pending": (i32, [vp, C.POINTER(vp), C.POINTER(u64)]),
+        "bt_pull_pending_parts": (i32, [vp, C.POINTER(u64), i32]),
         "bt_pull_drop": (i32, [vp]),
         "bt_pull_fill": (i32, [vp, vp, i32, vp, i32, i32, i32, C.POINTER(i32)]),
         "bt_shm_create": (i32, [C.c_char_p, u64, i32, C.POINTER(vp)]),
@@ -150,7 +151,7 @@ EXPORTS = ["bt_last_error", "bt_abi_version", "bt_scan_message", "bt_schema_crea
            "bt_ring_ingest", "bt_ring_submit_batch", "bt_ring_spill", "bt_ring_reap",
            "bt_rx_create", "bt_rx_destroy", "bt_rx_recv", "bt_rx_pending", "bt_rx_drop", "bt_rx_fill",
            "bt_rx_release_queued",
-           "bt_pull_create", "bt_pull_connect", "bt_pull_destroy", "bt_pull_recv", "bt_pull_pending",
+           "bt_pull_create", "bt_pull_connect", "bt_pull_destroy", "bt_pull_recv", "bt_pull_pending", "bt_pull_pending_parts",
            "bt_pull_drop", "bt_pull_fill",
            "bt_shm_create", "bt_shm_attach", "bt_shm_close", "bt_shm_nslots", "bt_shm_slot_bytes",
            "bt_shm_slot_ptr", "bt_shm_acquire", "bt_shm_release",

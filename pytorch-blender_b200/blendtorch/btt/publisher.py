@@ -6,9 +6,11 @@ a bounded send queue that blocks the caller when consumers are slow, and message
 ``pickle({'btid': btid, **kwargs})``.  It exists on the btt side so that synthetic producers
 (tests, benchmarks, simulators that are not Blender) speak the exact wire format.
 
-Opt-in extension for producers on the same host as their consumers: ``shm_slots=N`` sends every
-array of at least ``shm_threshold`` bytes through a shared-memory segment and only a reference
-through ZMQ (see shm.py).  Such messages are understood by this package, not by the reference.
+Opt-in extensions (understood by this package, not by the reference): ``shm_slots=N``, for producers
+on the same host as their consumers, sends every array of at least ``shm_threshold`` bytes through a
+shared-memory segment and only a reference through ZMQ (see shm.py); ``raw_parts=True``, for any
+producer, sends large arrays as separate zero-copy frames of a multipart message instead of pickling
+them (see wire.py).
 """
 import pickle
 
@@ -28,10 +30,13 @@ class DataPublisher:
         slots (the segment is created on the first large array and sized for it).
     shm_threshold: smallest array, in bytes, that goes through shared memory.
     shm_timeoutms: how long `publish` waits for a free slot before raising (consumers gone).
+    raw_parts: True = arrays of at least `raw_threshold` bytes travel as their own frames, sent
+        straight from the array's memory (no pickling copy, no pyzmq copy); the caller must not
+        modify a published array until it has been sent (pass a fresh array per frame, as renderers do).
     """
 
     def __init__(self, bind_address, btid=None, send_hwm=10, lingerms=0, protocol=None,
-                 shm_slots=0, shm_threshold=65536, shm_timeoutms=10000):
+                 shm_slots=0, shm_threshold=65536, shm_timeoutms=10000, raw_parts=False, raw_threshold=4096):
         self.ctx = zmq.Context()
         self.sock = self.ctx.socket(zmq.PUSH)
         self.sock.setsockopt(zmq.SNDHWM, send_hwm)
@@ -42,6 +47,7 @@ class DataPublisher:
         self.lingerms = lingerms
         self.protocol = pickle.DEFAULT_PROTOCOL if protocol is None else protocol  # == pyzmq default
         self.shm_slots, self.shm_threshold, self.shm_timeoutms = int(shm_slots), int(shm_threshold), int(shm_timeoutms)
+        self.raw_parts, self.raw_threshold = bool(raw_parts), int(raw_threshold)
         self._segment = None
 
     def _by_reference(self, array):
@@ -59,6 +65,10 @@ class DataPublisher:
             for k, v in data.items():
                 if isinstance(v, np.ndarray) and v.nbytes >= self.shm_threshold and not v.dtype.hasobject:
                     data[k] = self._by_reference(v)
+        if self.raw_parts:
+            from . import wire
+            self.sock.send_multipart(wire.pack(data, self.raw_threshold, self.protocol), copy=False)
+            return
         self.publish_raw(pickle.dumps(data, protocol=self.protocol))
 
     def publish_raw(self, data, copy=True):

@@ -65,6 +65,19 @@ class Receiver:
         N.check(N.lib.bt_rx_pending(self.handle, C.byref(p), C.byref(n)))
         return memoryview((C.c_uint8 * n.value).from_address(p.value)).cast("B")
 
+    def pending_parts(self):
+        """Frame sizes of the held message as far as this receiver has them (always one frame: see `more`)."""
+        return [len(self.pending())]
+
+    def more(self):
+        """True when the held frame is the first of a multipart message (raw-parts wire, wire.py) whose
+        other frames are still queued on the socket."""
+        return bool(self._sock.getsockopt(zmq.RCVMORE))
+
+    def recv_rest(self):
+        """The remaining frames of the message whose first frame is held."""
+        return self._sock.recv_multipart(copy=False)
+
     def drop(self):
         N.check(N.lib.bt_rx_drop(self.handle))
 
@@ -125,6 +138,21 @@ class DirectReceiver:
         p, n = C.c_void_p(), C.c_uint64()
         N.check(N.lib.bt_pull_pending(self.handle, C.byref(p), C.byref(n)))
         return memoryview((C.c_uint8 * n.value).from_address(p.value)).cast("B")
+
+    def pending_parts(self):
+        """Frame sizes of the held message: one for the reference wire, several for the raw-parts wire
+        (`pending` then spans all frames back to back)."""
+        sizes = (C.c_uint64 * 64)()
+        n = N.lib.bt_pull_pending_parts(self.handle, sizes, 64)
+        if n < 0:
+            N.check(n)
+        return [int(sizes[i]) for i in range(min(n, 64))]
+
+    def more(self):
+        return False     # this receiver always holds whole messages
+
+    def recv_rest(self):
+        return []
 
     def drop(self):
         N.check(N.lib.bt_pull_drop(self.handle))

@@ -20,6 +20,7 @@ import numpy as np
 
 from . import native as N
 from . import shm
+from . import wire
 
 _ALIGN = 256
 
@@ -57,9 +58,12 @@ class Schema:
         return self.handle is not None
 
     @classmethod
-    def from_message(cls, msg, batch):
-        """Derive the schema from the first message of a stream (bytes-like pickle)."""
+    def from_message(cls, msg, batch, sizes=None):
+        """Derive the schema from the first message of a stream (bytes-like pickle).  `sizes`: frame
+        sizes when `msg` holds a raw-parts message (wire.py), header frame first."""
         addr, n = N.buffer_address(msg)
+        if sizes is not None and len(sizes) > 1:
+            n = int(sizes[0])
         h = C.c_void_p()
         rc = N.lib.bt_schema_create(addr, n, batch, C.byref(h))
         if rc == N.BT_OK:
@@ -72,7 +76,7 @@ class Schema:
             return cls(batch, cols, handle=h)
         if rc not in (N.BT_E_UNSUPPORTED,):
             N.check(rc)
-        return cls.from_object(shm.resolve(pickle.loads(msg)), batch)
+        return cls.from_object(shm.resolve(wire.loads(msg, sizes)), batch)
 
     @classmethod
     def from_object(cls, obj, batch):

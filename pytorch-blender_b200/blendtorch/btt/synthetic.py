@@ -110,12 +110,14 @@ def write_recordings(prefix, config, n_files, frames_per_file, h=None, w=None, c
 
 
 def run_publisher(bind, btid, config, h, w, c=4, count=-1, pool=16, protocol=3, send_hwm=10,
-                  lingerms=5000, rate=0.0, shm_slots=0):
+                  lingerms=5000, rate=0.0, shm_slots=0, raw_parts=False):
     """Publish `count` messages (-1: until killed) from a pre-generated pool: pre-pickled for the
-    reference wire, arrays copied into shared-memory slots for the shared-memory wire."""
+    reference wire, arrays copied into shared-memory slots for the shared-memory wire, arrays sent as
+    their own frames for the raw-parts wire."""
     pub = DataPublisher(bind, btid=btid, send_hwm=send_hwm, lingerms=lingerms, protocol=protocol,
-                        shm_slots=shm_slots)
-    if shm_slots > 0:
+                        shm_slots=shm_slots, raw_parts=raw_parts)
+    by_object = shm_slots > 0 or raw_parts
+    if by_object:
         rng = rng_for(config, btid)
         objs = [message(rng, config, btid, i, h, w, c) for i in range(pool)]
         for o in objs:
@@ -125,7 +127,7 @@ def run_publisher(bind, btid, config, h, w, c=4, count=-1, pool=16, protocol=3, 
     i = 0
     try:
         while count < 0 or i < count:
-            if shm_slots > 0:
+            if by_object:
                 pub.publish(**objs[i % pool])
             else:
                 pub.publish_raw(msgs[i % len(msgs)], copy=False)
@@ -150,12 +152,14 @@ def main(argv=None):
     ap.add_argument("--protocol", type=int, default=3)
     ap.add_argument("--send-hwm", type=int, default=10)
     ap.add_argument("--shm-slots", type=int, default=0)
+    ap.add_argument("--raw-parts", action="store_true")
     a = ap.parse_args(argv)
     h, w, c = CONFIG_SHAPES.get(a.config, (480, 640, 4))
     h, w, c = a.height or h, a.width or w, a.channels or c
     import signal
     signal.signal(signal.SIGTERM, lambda *_: sys.exit(0))  # run `finally` blocks (unlink shared memory)
-    run_publisher(a.bind, a.btid, a.config, h, w, c, a.count, a.pool, a.protocol, a.send_hwm, shm_slots=a.shm_slots)
+    run_publisher(a.bind, a.btid, a.config, h, w, c, a.count, a.pool, a.protocol, a.send_hwm, shm_slots=a.shm_slots,
+                  raw_parts=a.raw_parts)
 
 
 if __name__ == "__main__":

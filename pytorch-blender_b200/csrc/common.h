@@ -68,6 +68,11 @@ struct PendingRef {
 };
 
 int scan_fields(const uint8_t* msg, uint64_t len, std::vector<bt_field>& out);
+// bt_field.payload_off of a BT_KIND_RAWREF field whose frame the receiver has already put in place
+constexpr uint64_t kLandedOff = ~0ull;
+// Raw-parts messages held as one buffer (frame 0 = pickled header, frames 1.. = array bytes, back to
+// back): point every BT_KIND_RAWREF field of the scanned header at its frame.
+int resolve_raw_parts(std::vector<bt_field>& f, const uint64_t* sizes, int nparts);
 uint64_t field_bytes(const bt_field& f);
 std::vector<bt_field>& tls_fields();
 

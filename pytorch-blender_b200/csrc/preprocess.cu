@@ -604,7 +604,9 @@ __global__ void __launch_bounds__(kThreads) k1_pixel(K1Args a, PlanarGeom g) {
           uint64_t off;
           if (CHW) off = ((uint64_t)bb[j] * a.Cout + c) * plane + (uint64_t)yy[j] * a.W + xx[j];
           else off = (((uint64_t)bb[j] * a.H + yy[j]) * a.W + xx[j]) * a.Cout + c;
-          dst[off] = o;
+          const T one[1] = {o};
+          if constexpr (sizeof(T) == 4) st_stream<T, 1>(dst + off, one);   // written once, never re-read here
+          else dst[off] = o;
           if (STATS) { float f = OutT<T>::as_float(o); acc.s[c] += f; acc.q[c] += (double)f * f; }
         }
       }

@@ -378,6 +378,18 @@ bool finish_array(const Scanner& s, int dtype, int data_idx, bt_field* f) {
   return true;
 }
 
+// numpy dtype.str ('<f4', '|u1') -> bt_dtype, -1 for what has no column type (big-endian, objects)
+int dtype_from_str(char endian, char code, int size) {
+  if (endian == '>' && size > 1) return -1;
+  switch (code) {
+    case 'u': return size == 1 ? BT_U8 : size == 2 ? BT_U16 : size == 4 ? BT_U32 : size == 8 ? BT_U64 : -1;
+    case 'i': return size == 1 ? BT_I8 : size == 2 ? BT_I16 : size == 4 ? BT_I32 : size == 8 ? BT_I64 : -1;
+    case 'f': return size == 2 ? BT_F16 : size == 4 ? BT_F32 : size == 8 ? BT_F64 : -1;
+    case 'b': return size == 1 ? BT_BOOL : -1;
+  }
+  return -1;
+}
+
 void classify(const Scanner& s, int idx, bt_field* f) {
   const Node& v = s.nodes[idx];
   f->kind = BT_KIND_OTHER;
@@ -390,6 +402,20 @@ void classify(const Scanner& s, int idx, bt_field* f) {
     case N_TUPLE: {
       // shared-memory wire marker: ("__btshm__", segment_name, slot, dtype_str, shape)
       const std::vector<int>& t = s.kidpool[v.kids];
+      if (t.size() == 4) {
+        // raw-parts wire marker: ("__btraw__", part_index, dtype_str, shape)
+        const Node& tag = s.nodes[t[0]];
+        const Node& part = s.nodes[t[1]];
+        const Node& dts = s.nodes[t[2]];
+        if (tag.k != N_STR || !s.span_eq(tag.off, tag.len, "__btraw__")) return;
+        if (part.k != N_INT || part.i < 1 || part.i > 1024 || dts.k != N_STR || dts.len != 3) return;
+        const int dt = dtype_from_str((char)s.p[dts.off], (char)s.p[dts.off + 1], (char)s.p[dts.off + 2] - '0');
+        if (dt < 0 || !parse_shape(s, t[3], f)) return;
+        f->kind = BT_KIND_RAWREF;
+        f->dtype = dt;
+        f->ival = part.i;
+        return;
+      }
       if (t.size() != 5) return;
       const Node& tag = s.nodes[t[0]];
       if (tag.k != N_STR || !s.span_eq(tag.off, tag.len, "__btshm__")) return;
@@ -398,16 +424,7 @@ void classify(const Scanner& s, int idx, bt_field* f) {
       const Node& dts = s.nodes[t[3]];
       if (name.k != N_STR || name.len == 0 || name.len >= BT_MAX_KEY || slot.k != N_INT || slot.i < 0) return;
       if (dts.k != N_STR || dts.len != 3) return;  // numpy dtype.str: '<f4', '|u1'
-      const char e = (char)s.p[dts.off], c0 = (char)s.p[dts.off + 1];
-      const int size = (char)s.p[dts.off + 2] - '0';
-      if (e == '>' && size > 1) return;
-      int dt = -1;
-      switch (c0) {
-        case 'u': dt = size == 1 ? BT_U8 : size == 2 ? BT_U16 : size == 4 ? BT_U32 : size == 8 ? BT_U64 : -1; break;
-        case 'i': dt = size == 1 ? BT_I8 : size == 2 ? BT_I16 : size == 4 ? BT_I32 : size == 8 ? BT_I64 : -1; break;
-        case 'f': dt = size == 2 ? BT_F16 : size == 4 ? BT_F32 : size == 8 ? BT_F64 : -1; break;
-        case 'b': dt = size == 1 ? BT_BOOL : -1; break;
-      }
+      const int dt = dtype_from_str((char)s.p[dts.off], (char)s.p[dts.off + 1], (char)s.p[dts.off + 2] - '0');
       if (dt < 0 || !parse_shape(s, t[4], f)) return;
       f->kind = BT_KIND_SHMREF;
       f->dtype = dt;
@@ -581,6 +598,18 @@ int stream_fields(const uint8_t* buf, std::vector<bt_field>& out) {
   return collect_fields(tls_scanner(), buf, out);
 }
 
+int resolve_raw_parts(std::vector<bt_field>& f, const uint64_t* sizes, int nparts) {
+  for (bt_field& fi : f) {
+    if (fi.kind != BT_KIND_RAWREF) continue;
+    if (fi.ival < 1 || fi.ival >= nparts) continue;   // stays unresolved: place_fields reports it
+    uint64_t off = 0;
+    for (int k = 0; k < (int)fi.ival; ++k) off += sizes[k];
+    fi.payload_off = off;
+    fi.payload_len = sizes[fi.ival];
+  }
+  return BT_OK;
+}
+
 std::vector<bt_field>& tls_fields() {
   static thread_local std::vector<bt_field> v;
   return v;
@@ -682,10 +711,17 @@ int place_fields(const bt_schema* s, uint8_t* base, int item, const uint8_t* msg
     uint8_t* dst = base + c.slot_off + c.item_bytes * (uint64_t)item;
     switch (c.kind) {
       case BT_KIND_NDARRAY: {
-        const bool by_ref = fi->kind == BT_KIND_SHMREF;
-        if ((fi->kind != BT_KIND_NDARRAY && !by_ref) || fi->dtype != c.dtype || fi->ndim != c.ndim || fi->fortran ||
+        const bool by_ref = fi->kind == BT_KIND_SHMREF, raw = fi->kind == BT_KIND_RAWREF;
+        if ((fi->kind != BT_KIND_NDARRAY && !by_ref && !raw) || fi->dtype != c.dtype || fi->ndim != c.ndim || fi->fortran ||
             memcmp(fi->shape, c.shape, sizeof(int64_t) * c.ndim) != 0 || field_bytes(*fi) != c.item_bytes)
           return fail(BT_E_SCHEMA, "field '%s' changed type or shape", c.key);
+        if (raw) {  // the bytes came as their own frame
+          if (fi->payload_len != c.item_bytes)
+            return fail(BT_E_SCHEMA, "field '%s': frame %lld of the message is missing or has the wrong size", c.key,
+                        (long long)fi->ival);
+          if (fi->payload_off != kLandedOff) copy_or_defer(dst, msg + fi->payload_off, c.item_bytes, tasks);
+          break;
+        }
         if (!by_ref) {
           if (fi->payload_off >= kExternalBase) {  // landed by the streaming receiver already
             const uint64_t e = fi->payload_off - kExternalBase;
@@ -765,10 +801,11 @@ int bt_schema_create(const uint8_t* first_msg, uint64_t len, int batch, bt_schem
     bt_column c;
     memset(&c, 0, sizeof c);
     memcpy(c.key, fi.key, BT_MAX_KEY);
-    c.kind = fi.kind == BT_KIND_SHMREF ? BT_KIND_NDARRAY : fi.kind;
+    c.kind = (fi.kind == BT_KIND_SHMREF || fi.kind == BT_KIND_RAWREF) ? BT_KIND_NDARRAY : fi.kind;
     switch (fi.kind) {
       case BT_KIND_NDARRAY:
       case BT_KIND_SHMREF:
+      case BT_KIND_RAWREF:
         if (fi.fortran) { delete s; return fail(BT_E_UNSUPPORTED, "field '%s' is Fortran-ordered", fi.key); }
         c.dtype = fi.dtype; c.ndim = fi.ndim;
         memcpy(c.shape, fi.shape, sizeof c.shape);

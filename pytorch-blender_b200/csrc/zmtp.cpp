@@ -11,9 +11,10 @@
 //
 // Wire compatibility: the peers are unmodified ZMQ PUSH sockets (btb/publisher.py:21-27: PUSH, bind).
 // Implemented: ZMTP 3.0/3.1 greeting, NULL security handshake (READY with Socket-Type=PULL),
-// single-part messages, commands are skipped, reconnect with back-off, fair round-robin over peers,
-// tcp:// and ipc:// endpoints.  Anything else (multipart messages, other mechanisms) is reported and
-// the caller falls back to the libzmq receiver (rx.cpp).
+// single-frame messages (the reference wire) and multi-frame ones (the opt-in raw-parts wire: pickled
+// header frame + one frame per large array, received straight into the slot), commands are skipped,
+// reconnect with back-off, fair round-robin over peers, tcp:// and ipc:// endpoints.  Other security
+// mechanisms are reported and the caller falls back to the libzmq receiver (rx.cpp).
 #include <arpa/inet.h>
 #include <fcntl.h>
 #include <netdb.h>
@@ -26,6 +27,7 @@
 #include <unistd.h>
 
 #include <cerrno>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -274,9 +276,11 @@ struct bt_pull {
   std::vector<Peer> peers;
   size_t rr = 0;
   std::vector<uint8_t> cb;    // message in progress, large payloads cut out
-  std::vector<uint8_t> held;  // a complete message kept for the caller
+  std::vector<uint8_t> held;  // a complete message kept for the caller (all frames back to back)
+  std::vector<uint64_t> held_parts;  // sizes of its frames (one entry for ordinary single-frame messages)
   bool has_held = false;
   std::vector<External> ext;
+  std::vector<uint8_t> spill;   // frames of a raw-parts message that could not go straight to the slot
   std::vector<pollfd> pfds;
   uint64_t messages = 0, bytes = 0;
 };
@@ -370,8 +374,9 @@ int wait_readable(bt_pull* q, int timeout_ms) {
   }
 }
 
-// Read one frame header.  *is_msg = 0 for a command (skipped), 1 for a message of `*size` bytes.
-int read_frame_header(Peer& p, int* is_msg, uint64_t* size) {
+// Read one frame header.  *is_msg = 0 for a command (skipped), 1 for a message frame of `*size` bytes;
+// *more = 1 when further frames of the same message follow (raw-parts wire).
+int read_frame_header(Peer& p, int* is_msg, uint64_t* size, int* more) {
   uint8_t h[9];
   int rc = take(p, h, 2, kIoTimeoutMs, true);
   if (rc != BT_OK) return rc;
@@ -394,18 +399,44 @@ int read_frame_header(Peer& p, int* is_msg, uint64_t* size) {
     *is_msg = 0;
     return BT_OK;
   }
-  if (h[0] & 0x01) return bt::fail(BT_E_IO, "multipart messages are not part of the blendtorch wire (publisher.py:43)");
   if (sz > (1ull << 40)) return bt::fail(BT_E_IO, "implausible message size");
   *is_msg = 1;
   *size = sz;
+  *more = h[0] & 0x01;
   return BT_OK;
 }
 
-// Whole message into q->held.
-int read_whole(bt_pull* q, Peer& p, uint64_t size) {
+constexpr int kMaxParts = 64;            // frames per message the endpoint accepts
+constexpr uint64_t kMaxHeader = 1 << 20;  // pickled header frame of a raw-parts message
+
+// Append the remaining frames of a multipart message to q->held (sizes to q->held_parts).
+int read_more_frames(bt_pull* q, Peer& p) {
+  while (true) {
+    int is_msg = 0, more = 0;
+    uint64_t size = 0;
+    int rc = read_frame_header(p, &is_msg, &size, &more);
+    if (rc != BT_OK) return rc;
+    if (!is_msg) continue;
+    if ((int)q->held_parts.size() >= kMaxParts) return bt::fail(BT_E_IO, "message has more than %d frames", kMaxParts);
+    const size_t at = q->held.size();
+    q->held.resize(at + size);
+    rc = take(p, q->held.data() + at, size, kIoTimeoutMs, size <= kAheadBytes);
+    if (rc != BT_OK) return rc;
+    q->held_parts.push_back(size);
+    if (!more) return BT_OK;
+  }
+}
+
+// Whole message (every frame) into q->held.
+int read_whole(bt_pull* q, Peer& p, uint64_t size, int more) {
   q->held.resize(size);
+  q->held_parts.assign(1, size);
   int rc = take(p, q->held.data(), size, kIoTimeoutMs, size <= kAheadBytes);
   if (rc != BT_OK) return rc;
+  if (more) {
+    rc = read_more_frames(q, p);
+    if (rc != BT_OK) return rc;
+  }
   q->has_held = true;
   return BT_OK;
 }
@@ -428,6 +459,7 @@ int rebuild_into_held(bt_pull* q, Peer& p, uint64_t msg_size, uint64_t consumed)
   out.resize(msg_size);
   int rc = take(p, out.data() + have, msg_size - have, kIoTimeoutMs, msg_size - have <= kAheadBytes);
   if (rc != BT_OK) return rc;
+  q->held_parts.assign(1, msg_size);
   q->has_held = true;
   return BT_OK;
 }
@@ -499,6 +531,100 @@ int receive_streaming(bt_pull* q, Peer& p, uint64_t msg_size, bt_ring* ring, int
   return why;
 }
 
+// Raw-parts message (DataPublisher(raw_parts=True)): frame 0 is the pickled header, in which every
+// large array is a ("__btraw__", k, dtype, shape) marker; frame k carries that array's bytes.  Frames
+// that match a schema column are received straight into the slot -- no scan of the payload, no
+// intermediate buffer on either side.  Return values as receive_streaming; on BT_E_UNSUPPORTED /
+// BT_E_SCHEMA the whole message (all frames, back to back) is in q->held, sizes in q->held_parts.
+int receive_raw_parts(bt_pull* q, Peer& p, uint64_t header_size, bt_ring* ring, int slot, const bt_schema* schema, int item) {
+  if (header_size > kMaxHeader) {
+    int rc = read_whole(q, p, header_size, 1);
+    if (rc != BT_OK) return rc;
+    return bt::fail(BT_E_UNSUPPORTED, "header frame of %llu bytes", (unsigned long long)header_size);
+  }
+  q->cb.resize(header_size);
+  int rc = take(p, q->cb.data(), header_size, kIoTimeoutMs, true);
+  if (rc != BT_OK) return rc;
+  std::vector<bt_field>& f = bt::tls_fields();
+  int why = bt::scan_fields(q->cb.data(), header_size, f);
+  std::string reason = why == BT_OK ? std::string() : bt::last_error_ref();
+  uint8_t* base = bt::ring_slot_base(ring, slot);
+  struct Part { uint64_t size; const uint8_t* landed; uint64_t spill_off; };
+  std::vector<Part> parts;
+  q->spill.clear();
+  int more = 1;
+  while (more) {
+    int is_msg = 0;
+    uint64_t size = 0;
+    rc = read_frame_header(p, &is_msg, &size, &more);
+    if (rc != BT_OK) return rc;
+    if (!is_msg) { more = 1; continue; }
+    const int index = (int)parts.size() + 1;
+    if (index >= kMaxParts) return bt::fail(BT_E_IO, "message has more than %d frames", kMaxParts);
+    uint8_t* dst = nullptr;
+    bt_field* owner = nullptr;
+    if (why == BT_OK) {
+      for (bt_field& fi : f)
+        if (fi.kind == BT_KIND_RAWREF && fi.ival == index && fi.payload_len == 0) { owner = &fi; break; }
+      if (owner) {
+        for (const bt_column& c : schema->cols) {
+          if (strcmp(c.key, owner->key) != 0) continue;
+          if (c.kind == BT_KIND_NDARRAY && c.dtype == owner->dtype && c.ndim == owner->ndim && !owner->fortran &&
+              memcmp(c.shape, owner->shape, sizeof(int64_t) * c.ndim) == 0 && c.item_bytes == size)
+            dst = base + c.slot_off + c.item_bytes * (uint64_t)item;
+          break;
+        }
+      }
+      if (!dst) {
+        why = BT_E_SCHEMA;
+        char msg[160];
+        snprintf(msg, sizeof msg, "frame %d of %llu bytes matches no column of the schema", index, (unsigned long long)size);
+        reason = msg;
+      }
+    }
+    if (dst) {
+      rc = take(p, dst, size, kIoTimeoutMs, false);
+      if (rc != BT_OK) return rc;
+      owner->payload_off = bt::kLandedOff;
+      owner->payload_len = size;
+      parts.push_back(Part{size, dst, 0});
+    } else {
+      const uint64_t at = q->spill.size();
+      q->spill.resize(at + size);
+      rc = take(p, q->spill.data() + at, size, kIoTimeoutMs, size <= kAheadBytes);
+      if (rc != BT_OK) return rc;
+      parts.push_back(Part{size, nullptr, at});
+    }
+  }
+  if (why == BT_OK) {
+    rc = bt::ring_place(ring, slot, schema, item, q->cb.data(), f);
+    if (rc == BT_OK) return BT_OK;
+    why = rc == BT_E_SCHEMA ? BT_E_SCHEMA : BT_E_UNSUPPORTED;
+    reason = bt::last_error_ref();
+  }
+  // hand the message to the caller's decode: every frame back to back
+  q->held.assign(q->cb.begin(), q->cb.end());
+  q->held_parts.assign(1, header_size);
+  for (const Part& part : parts) {
+    const uint8_t* src = part.landed ? part.landed : q->spill.data() + part.spill_off;
+    q->held.insert(q->held.end(), src, src + part.size);
+    q->held_parts.push_back(part.size);
+  }
+  q->has_held = true;
+  bt::last_error_ref() = reason;
+  return why == BT_E_SCHEMA ? BT_E_SCHEMA : BT_E_UNSUPPORTED;
+}
+
+// Place the held message (received before the schema existed) as item `item` of the slot.
+int ingest_held(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, int item) {
+  if (q->held_parts.size() <= 1) return bt_ring_ingest(ring, slot, schema, item, q->held.data(), q->held.size());
+  std::vector<bt_field>& f = bt::tls_fields();
+  int rc = bt::scan_fields(q->held.data(), q->held_parts[0], f);
+  if (rc != BT_OK) return rc;
+  bt::resolve_raw_parts(f, q->held_parts.data(), (int)q->held_parts.size());
+  return bt::ring_place(ring, slot, schema, item, q->held.data(), f);
+}
+
 }  // namespace
 
 extern "C" {
@@ -538,10 +664,10 @@ int bt_pull_recv(bt_pull* q, int timeout_ms) {
     const int i = wait_readable(q, now >= deadline ? 0 : (int)(deadline - now));
     if (i < 0) return BT_E_TIMEOUT;
     Peer& p = q->peers[i];
-    int is_msg = 0;
+    int is_msg = 0, more = 0;
     uint64_t size = 0;
-    int rc = read_frame_header(p, &is_msg, &size);
-    if (rc == BT_OK && is_msg) rc = read_whole(q, p, size);
+    int rc = read_frame_header(p, &is_msg, &size, &more);
+    if (rc == BT_OK && is_msg) rc = read_whole(q, p, size, more);
     if (rc != BT_OK) { close_peer(p); continue; }
     if (is_msg) return BT_OK;
   }
@@ -559,6 +685,14 @@ int bt_pull_pending(bt_pull* q, const uint8_t** data, uint64_t* len) {
   return BT_OK;
 }
 
+int bt_pull_pending_parts(bt_pull* q, uint64_t* sizes, int max_parts) {
+  if (!q || (max_parts > 0 && !sizes)) return bt::fail(BT_E_INVALID, "bt_pull_pending_parts: bad arguments");
+  if (!q->has_held) return bt::fail(BT_E_INVALID, "no message is held");
+  const int n = (int)q->held_parts.size();
+  for (int i = 0; i < n && i < max_parts; ++i) sizes[i] = q->held_parts[i];
+  return n;
+}
+
 int bt_pull_drop(bt_pull* q) {
   if (!q) return bt::fail(BT_E_INVALID, "null receiver");
   q->has_held = false;
@@ -572,7 +706,7 @@ int bt_pull_fill(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, i
   *n_done = 0;
   while (*n_done < max_items) {
     if (q->has_held) {  // the first message of the stream, received before the schema existed
-      int rc = bt_ring_ingest(ring, slot, schema, first_item + *n_done, q->held.data(), q->held.size());
+      int rc = ingest_held(q, ring, slot, schema, first_item + *n_done);
       if (rc != BT_OK) return rc;
       q->has_held = false;
       ++*n_done;
@@ -581,12 +715,13 @@ int bt_pull_fill(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, i
     const int i = wait_readable(q, slice_ms);
     if (i < 0) return BT_E_TIMEOUT;
     Peer& p = q->peers[i];
-    int is_msg = 0;
+    int is_msg = 0, more = 0;
     uint64_t size = 0;
-    int rc = read_frame_header(p, &is_msg, &size);
+    int rc = read_frame_header(p, &is_msg, &size, &more);
     if (rc != BT_OK) { close_peer(p); continue; }
     if (!is_msg) continue;
-    rc = receive_streaming(q, p, size, ring, slot, schema, first_item + *n_done);
+    rc = more ? receive_raw_parts(q, p, size, ring, slot, schema, first_item + *n_done)
+              : receive_streaming(q, p, size, ring, slot, schema, first_item + *n_done);
     if (rc == BT_E_UNSUPPORTED || rc == BT_E_SCHEMA) return rc;  // message is held for the caller
     if (rc != BT_OK) { close_peer(p); continue; }
     q->messages++;

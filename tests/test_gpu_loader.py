@@ -361,3 +361,45 @@ def test_resident_recording_limits_and_projection(tmp_path):
         btt.DeviceLoader(btt.FileDataset(str(tmp_path / "c3"), item_transform=lambda x: x), device=DEV, cache="device")
     with pytest.raises(ValueError):
         btt.DeviceLoader(btt.RemoteIterableDataset(["tcp://127.0.0.1:1"]), device=DEV, cache="device")
+
+
+def _raw_publisher(addr, btid, count, h, w):
+    S.run_publisher(addr, btid, 2, h, w, 4, count=count, pool=8, protocol=3, lingerms=10000, raw_parts=True)
+
+
+@pytest.mark.parametrize("transport,receivers", [("direct", 2), ("zmq", 1)])
+def test_stream_raw_parts_wire(transport, receivers):
+    """Opt-in raw-parts wire (wire.py): frames go from the socket straight into the staging slot with the
+    direct receiver (no compatibility decodes), and through the Python decode with pyzmq's socket."""
+    H, W, pubs, per_pub = 64, 128, 2, 16
+    addrs = ["tcp://127.0.0.1:%d" % _free_port() for _ in range(pubs)]
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=_raw_publisher, args=(a, i, -1, H, W), daemon=True) for i, a in enumerate(addrs)]
+    for p in procs:
+        p.start()
+    try:
+        total = per_pub * pubs
+        ds = btt.RemoteIterableDataset(addrs, max_items=total, timeoutms=30000)
+        dl = btt.DeviceLoader(ds, batch_size=4, device=DEV, num_receivers=receivers, keep_raw=True, transport=transport,
+                              preprocess=btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5))
+        expected = {}
+        for btid in range(pubs):
+            rng = S.rng_for(2, btid)
+            for i in range(8):
+                expected[(btid, i)] = S.message(rng, 2, btid, i, H, W)
+        n = 0
+        for b in dl:
+            raw = b["image_raw"].cpu().numpy()
+            np.testing.assert_array_equal(b["image"].cpu().numpy(),
+                                          opre.preprocess_batch(list(raw), flip=True, gamma=2.2, mean=127.5, std=127.5))
+            for i in range(len(raw)):
+                m = expected[(int(b["btid"][i]), int(b["frameid"][i]))]
+                np.testing.assert_array_equal(raw[i], m["image"])
+                np.testing.assert_array_equal(b["bbox"][i].cpu().numpy(), m["bbox"])
+                n += 1
+        assert n == total
+        assert (dl.stats["compat_items"] == 0) == (transport == "direct")
+    finally:
+        for p in procs:
+            p.terminate()
+            p.join(timeout=10)

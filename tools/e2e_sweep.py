@@ -29,9 +29,11 @@ def main():
         shm_slots = combo[3] if len(combo) > 3 else 0
         bench.PUBLISHERS = combo[4] if len(combo) > 4 else 5
         rxmode = combo[5] if len(combo) > 5 else "auto"
-        images, sec, h2d, d2h = bench.e2e_leg(torch, btt, dev, 600, 10, _S(), transport, recv, io, shm_slots, rxmode)
+        raw = len(combo) > 6 and combo[6] == "raw"
+        images, sec, h2d, d2h = bench.e2e_leg(torch, btt, dev, 600, 10, _S(), transport, recv, io, shm_slots, rxmode,
+                                              raw_parts=raw)
         r = {"transport": transport, "rx": rxmode, "receivers": recv, "io_threads": io, "shm_slots": shm_slots,
-             "publishers": bench.PUBLISHERS, "images_per_s": images / sec,
+             "publishers": bench.PUBLISHERS, "raw_parts": raw, "images_per_s": images / sec,
              "GBps": images / sec * 1228800 / 1e9}
         print(json.dumps(r), flush=True)
         res.append(r)
