@@ -94,6 +94,25 @@ def _mutations(rng, good):
     return [_frame(bytes(b))]
 
 
+def _raw_parts_mutations(rng, k):
+    """Raw-parts framing (wire.py) gone wrong."""
+    from blendtorch.btt import wire
+    frames = wire.pack(_msg(k))
+    hdr, img = frames[0], frames[1].tobytes()
+    kind = k % 5
+    if kind == 0:   # the array frame is one byte short
+        return [_frame(hdr, 1), _frame(img[:-1])]
+    if kind == 1:   # the header promises a frame that never comes
+        return [_frame(hdr, 0)]
+    if kind == 2:   # more frames than the endpoint accepts
+        return [_frame(hdr, 1)] + [_frame(b"x", 1)] * 80 + [_frame(b"x")]
+    if kind == 3:   # header refers to frame 7 of 2
+        bad = pickle.dumps({"btid": 0, "image": ("__btraw__", 7, "|u1", (40, 50, 4)), "frameid": k}, protocol=3)
+        return [_frame(bad, 1), _frame(img)]
+    # a well-formed one, followed by a frame header cut off in the middle
+    return [_frame(hdr, 1), _frame(img), bytes([0x02, 0, 0])]
+
+
 def test_hostile_peer_never_wedges_the_receiver():
     rng = np.random.default_rng(99)
     n_bad = 60
@@ -102,7 +121,7 @@ def test_hostile_peer_never_wedges_the_receiver():
         proto = 3 + k % 3
         good = pickle.dumps(_msg(k), protocol=proto)
         # a good message first, so that a schema exists; then the mutated one
-        scripts.append([_frame(good)] + _mutations(rng, good))
+        scripts.append([_frame(good)] + (_raw_parts_mutations(rng, k) if k % 4 == 3 else _mutations(rng, good)))
     final = [_frame(pickle.dumps(_msg(1000 + i), protocol=3)) for i in range(5)]
     scripts.append(final)
     peer = _Peer(scripts)
