@@ -100,7 +100,12 @@ def main():
     ap.add_argument("--receivers", type=int, default=4)
     ap.add_argument("--publishers", type=int, default=5)
     ap.add_argument("--arms", default="resident,device_loader,reference_style")
+    ap.add_argument("--switch-interval", type=float, default=0.0,
+                    help="sys.setswitchinterval for the run (seconds; 0 = leave Python's 5 ms): the loader's receiver "
+                         "threads need the interpreter lock for ~0.1 ms per batch, the training loop holds it")
     a = ap.parse_args()
+    if a.switch_interval > 0:
+        sys.setswitchinterval(a.switch_interval)
     dev = torch.device("cuda", 0)
     torch.backends.cudnn.benchmark = True
     model = discriminator().to(dev).to(memory_format=torch.channels_last)
