@@ -177,6 +177,12 @@ int bt_ring_submit_batch(bt_ring* r, int slot, const bt_schema* s, int n_items, 
 int bt_ring_spill(bt_ring* r, int slot, const bt_schema* s);
 /* Non-blocking: release references of slots whose copies have completed. */
 int bt_ring_reap(bt_ring* r);
+/* Batch assembly by DMA from a recording kept in page-locked host memory (no reference counterpart:
+ * file.py:100-108 re-reads and re-unpickles the file every epoch): row index[i] of the host array
+ * `src_host` (rows of row_bytes) goes to row i of `dst_dev`, on `stream`; neighbouring source rows are
+ * merged into one copy.  No CPU touches the payload.  src_host must be page-locked for the copies to
+ * be asynchronous. */
+int bt_gather_h2d(void* dst_dev, const void* src_host, uint64_t row_bytes, const int64_t* index, int n, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Receive loop in C.

@@ -26,6 +26,7 @@ which gathers its frames straight from the resident set.
 import pickle
 import queue
 import threading
+import time
 import warnings
 import ctypes as C
 
@@ -119,7 +120,7 @@ class _Stager:
         self.schema = schema
         self.device = device
         self.projections = projections
-        self.ring = Ring(schema.slot_bytes, depth, device.index)
+        self.ring = Ring(schema.slot_bytes, depth, device.index) if depth > 0 else None   # 0: batches come by DMA gather
         self.stream = torch.cuda.Stream(device)
         torch.cuda.set_stream(self.stream)      # thread-local: this receiver thread only
         self._stream_handle = C.c_void_p(self.stream.cuda_stream)
@@ -143,14 +144,16 @@ class _Stager:
     def ingest(self, slot, item, msg, host_rows):
         self.ring.ingest(slot, self.schema, item, msg, host_rows)
 
-    def finish(self, slot, n, host_rows, cache=None, idx=None):
+    def finish(self, slot, n, host_rows, cache=None, idx=None, fill=None):
         sch = self.schema
         used = 0
         for _, off, ib, _, _, _ in self.plan:
             used = max(used, off + n * ib)
         batch = {}
         raw = torch.empty(max(used, 1), dtype=torch.uint8, device=self.device)
-        if used:
+        if used and fill is not None:
+            fill(raw.data_ptr(), self._stream_handle)      # e.g. rows gathered from a pinned recording
+        elif used:
             self.ring.submit_batch(slot, sch, n, raw.data_ptr(), self._stream_handle)
         keep = [raw]                       # distinct storages the consumer stream must know about
         base = raw.data_ptr()
@@ -182,8 +185,57 @@ class _Stager:
 
     def close(self):
         self.stream.synchronize()
-        self.ring.close()
+        if self.ring is not None:
+            self.ring.close()
         self.schema.close()
+
+
+class _HostCache:
+    """A recording kept in page-locked host memory: the batch layout with batch = len(dataset), i.e. one
+    column per field whose rows are dataset indices.  Filled once, straight from the mmap'ed files (one
+    CPU copy per byte, on the worker pool); after that every batch of every epoch is assembled on the
+    device by DMA (`bt_gather_h2d`): no file access, no scan, no CPU copy."""
+
+    def __init__(self, first_msg, n):
+        self.n = n
+        self.schema = Schema.from_message(first_msg, n)
+        if not self.schema.native or self.schema.host_keys:
+            self.schema.close()
+            raise ValueError("messages need the Python decode")
+        self.mem = torch.empty(self.schema.slot_bytes, dtype=torch.uint8, pin_memory=True)
+        self.ptr = self.mem.data_ptr()
+        self.nbytes = self.schema.slot_bytes
+
+    @staticmethod
+    def bytes_needed(first_msg, n):
+        sch = Schema.from_message(first_msg, n)
+        try:
+            return sch.slot_bytes
+        finally:
+            sch.close()
+
+    def fill(self, ds, threads):
+        """Every message of every file to its row; False if one of them needs the Python decode."""
+        base = 0
+        for d in ds.datasets:
+            reader, count = d.reader, len(d.reader)
+            for c0 in range(0, count, 512):
+                local = np.arange(c0, min(c0 + 512, count))
+                addrs, lens = reader.spans(local)
+                if self.schema.ingest_many(self.ptr, base + c0, addrs, lens, threads) >= 0:
+                    return False
+            base += count
+        return True
+
+    def gather(self, plan, idx, raw_ptr, stream_handle):
+        """Rows `idx` of every column to the device batch at raw_ptr (the batch layout of `plan`)."""
+        idx = np.ascontiguousarray(idx, dtype=np.int64)
+        for col, (_, off, ib, _, _, _) in zip(self.schema.columns, plan):
+            N.check(N.lib.bt_gather_h2d(raw_ptr + off, self.ptr + col.slot_off, ib, idx.ctypes.data, len(idx), stream_handle))
+
+    def close(self):
+        self.schema.close()
+        self.mem = None
 
 
 class DeviceLoader:
@@ -216,8 +268,12 @@ class DeviceLoader:
         first epoch fills it on the way through, every later epoch is served from it -- no file, host
         or PCIe traffic; K1 gathers the sampler's frames straight from the resident set.  Only for
         `FileDataset` without an item_transform (a transform may differ from epoch to epoch).
-    cache_bytes: device-memory budget of the cache (default: 80 % of what is free when the layout of
-        the recording becomes known).  A recording that does not fit is replayed uncached, with a warning.
+        'host' keeps it in page-locked host memory instead (for recordings larger than HBM): it is
+        read from the files once, before the first batch, and every batch of every epoch is then
+        assembled on the device by DMA from there -- no CPU copy per epoch.
+    cache_bytes: memory budget of the cache (default: 80 % of the free device memory when the layout of
+        the recording becomes known; half of the available host memory for 'host').  A recording that
+        does not fit is replayed uncached, with a warning.
     """
 
     def __init__(self, dataset, batch_size=1, shuffle=False, drop_last=False, device="cuda",
@@ -256,10 +312,11 @@ class DeviceLoader:
         self.transport = transport
         self._epoch = 0
         self._stagers = {}
-        if cache not in (None, "device"):
-            raise ValueError("cache must be None or 'device'")
+        if cache not in (None, "device", "host"):
+            raise ValueError("cache must be None, 'device' or 'host'")
         self.cache_mode, self.cache_bytes = cache, cache_bytes
         self._cache, self._cache_off, self._cache_lock = None, False, threading.Lock()
+        self._host = None
         self.stats = {"batches": 0, "items": 0, "bytes_h2d": 0, "kernels": 0, "compat_items": 0,
                       "resident_batches": 0, "cache_bytes": 0}
         if isinstance(dataset, RemoteIterableDataset):
@@ -271,7 +328,7 @@ class DeviceLoader:
         else:
             raise TypeError("DeviceLoader takes a btt.RemoteIterableDataset or a btt.FileDataset")
         if cache is not None and (self._mode != "replay" or dataset.has_custom_item()):
-            raise ValueError("cache='device' is for FileDataset replay without an item_transform")
+            raise ValueError("cache=%r is for FileDataset replay without an item_transform" % cache)
 
     def __len__(self):
         if self._mode == "replay":
@@ -284,7 +341,7 @@ class DeviceLoader:
         return n // self.batch_size if self.drop_last else -(-n // self.batch_size)
 
     # ---- producers --------------------------------------------------------------------------
-    def _new_stager(self, first_msg, rid=0, sizes=None):
+    def _new_stager(self, first_msg, rid=0, sizes=None, depth=None):
         """Stager for the stream that starts with `first_msg`.  Pinned rings are expensive to create
         (page-locking hundreds of MB takes longer than an epoch of small recordings), so a stager
         is kept per producer and reused by later epochs while the layout stays the same."""
@@ -293,8 +350,9 @@ class DeviceLoader:
             c = schema.column(key)  # KeyError: the named image field is not in the messages
             if c.dtype != np.uint8:
                 raise TypeError("field %r is %s; preprocessing takes uint8 frames" % (key, c.dtype))
+        depth = self.ring_depth if depth is None else depth
         sig = (schema.native, tuple((c.key, c.kind, c.dtype.str, c.shape, c.slot_off) for c in schema.columns),
-               schema.host_keys)
+               schema.host_keys, depth)
         cached = self._stagers.get(rid)
         if cached is not None and cached[0] == sig:
             schema.close()
@@ -303,7 +361,7 @@ class DeviceLoader:
             return stager
         if cached is not None:
             cached[1].close()
-        stager = _Stager(schema, self.device, self.ring_depth, self.specs, self.keep_raw, self.projections)
+        stager = _Stager(schema, self.device, depth, self.specs, self.keep_raw, self.projections)
         self._stagers[rid] = (sig, stager)
         return stager
 
@@ -329,10 +387,14 @@ class DeviceLoader:
         if self._cache is not None:
             torch.cuda.synchronize(self.device)    # readers of the resident rows may still be running
             self._cache = None
+        if self._host is not None:
+            torch.cuda.synchronize(self.device)    # copies out of the pinned recording may still be running
+            self._host.close()
+            self._host = None
 
     def _resident(self, schema):
         """The cache the producers fill, created when the first producer knows the layout."""
-        if self.cache_mode is None or self._cache_off:
+        if self.cache_mode != "device" or self._cache_off:
             return None
         with self._cache_lock:
             if self._cache is None and not self._cache_off:
@@ -356,8 +418,37 @@ class DeviceLoader:
         except Exception:
             pass
 
-    def _emit(self, out_q, stop, stager, slot, n, host_rows, cache=None, idx=None):
-        item = stager.finish(slot, n, host_rows, cache, idx)
+    def _fill_host_cache(self):
+        """cache='host': read the whole recording into page-locked memory (once)."""
+        ds = self.dataset
+        n = len(ds)
+        if n == 0:
+            self._cache_off = True
+            return
+        first = ds.datasets[0].reader.raw(0)
+        t0 = time.perf_counter()
+        try:
+            need = _HostCache.bytes_needed(first, n)
+            budget = self.cache_bytes
+            if budget is None:
+                import psutil
+                budget = psutil.virtual_memory().available // 2
+            if need > budget:
+                raise ValueError("recording needs %d bytes of page-locked memory, cache budget is %d" % (need, budget))
+            host = _HostCache(first, n)
+            if not host.fill(ds, max(self.ingest_threads, 1)):
+                host.close()
+                raise ValueError("a message needs the Python decode")
+        except ValueError as e:
+            self._cache_off = True
+            warnings.warn("%s: replaying uncached" % e)
+            return
+        self._host = host
+        self.stats["cache_bytes"] = host.nbytes
+        self.stats["cache_fill_s"] = time.perf_counter() - t0
+
+    def _emit(self, out_q, stop, stager, slot, n, host_rows, cache=None, idx=None, fill=None):
+        item = stager.finish(slot, n, host_rows, cache, idx, fill)
         self.stats["bytes_h2d"] += stager.item_bytes * n
         while not stop.is_set():
             try:
@@ -568,6 +659,15 @@ class DeviceLoader:
                 idx = order[start:start + B]
                 if len(idx) < B and self.drop_last:
                     break
+                if self._host is not None:
+                    # the recording is in page-locked memory: this batch is a handful of DMA copies
+                    if stager is None:
+                        stager = self._new_stager(readers[0].raw(0), rid, depth=0)
+                    host, plan = self._host, stager.plan
+                    if not self._emit(out_q, stop, stager, None, len(idx), {}, None, None,
+                                      lambda ptr, st, idx=idx: host.gather(plan, idx, ptr, st)):
+                        return
+                    continue
                 fidx = np.searchsorted(cum, idx, side="right")
                 local = idx - np.where(fidx > 0, cum[np.maximum(fidx - 1, 0)], 0)
                 if custom:
@@ -675,6 +775,8 @@ class DeviceLoader:
                 yield from self._resident_epoch(order)
                 return
             self._epoch -= 1
+        if self.cache_mode == "host" and self._host is None and not self._cache_off:
+            self._fill_host_cache()
         stop = threading.Event()
         if self._mode == "stream":
             n_prod, target = self.num_receivers, self._stream_producer

@@ -102,6 +102,7 @@ def _load():
         "bt_ring_submit_batch": (i32, [vp, i32, vp, i32, vp, vp]),
         "bt_ring_spill": (i32, [vp, i32, vp]),
         "bt_ring_reap": (i32, [vp]),
+        "bt_gather_h2d": (i32, [vp, vp, u64, vp, i32, vp]),
         "bt_rx_create": (i32, [vp, vp, C.POINTER(vp)]),
         "bt_rx_destroy": (i32, [vp]),
         "bt_rx_recv": (i32, [vp, i32]),
@@ -148,7 +149,7 @@ EXPORTS = ["bt_last_error", "bt_abi_version", "bt_scan_message", "bt_schema_crea
            "bt_schema_num_columns", "bt_schema_column", "bt_schema_slot_bytes", "bt_schema_ingest",
            "bt_schema_ingest_many", "bt_ring_create", "bt_ring_destroy", "bt_ring_depth",
            "bt_ring_slot_bytes", "bt_ring_slot_ptr", "bt_ring_acquire", "bt_ring_submit", "bt_ring_wait",
-           "bt_ring_ingest", "bt_ring_submit_batch", "bt_ring_spill", "bt_ring_reap",
+           "bt_ring_ingest", "bt_ring_submit_batch", "bt_ring_spill", "bt_ring_reap", "bt_gather_h2d",
            "bt_rx_create", "bt_rx_destroy", "bt_rx_recv", "bt_rx_pending", "bt_rx_drop", "bt_rx_fill",
            "bt_rx_release_queued",
            "bt_pull_create", "bt_pull_connect", "bt_pull_destroy", "bt_pull_recv", "bt_pull_pending", "bt_pull_pending_parts",

@@ -244,6 +244,23 @@ int bt_device_count(int* n) {
   return BT_OK;
 }
 
+int bt_gather_h2d(void* dst_dev, const void* src_host, uint64_t row_bytes, const int64_t* index, int n, void* stream) {
+  if (!dst_dev || !src_host || !index || n < 0 || row_bytes == 0) return bt::fail(BT_E_INVALID, "bt_gather_h2d: bad arguments");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  uint8_t* dst = static_cast<uint8_t*>(dst_dev);
+  const uint8_t* src = static_cast<const uint8_t*>(src_host);
+  int i = 0;
+  while (i < n) {
+    if (index[i] < 0) return bt::fail(BT_E_INVALID, "bt_gather_h2d: negative row index");
+    int j = i + 1;
+    while (j < n && index[j] == index[j - 1] + 1) ++j;   // rows that are neighbours in the source: one copy
+    BT_CUDA_TRY(cudaMemcpyAsync(dst + (uint64_t)i * row_bytes, src + (uint64_t)index[i] * row_bytes,
+                                (uint64_t)(j - i) * row_bytes, cudaMemcpyHostToDevice, st));
+    i = j;
+  }
+  return BT_OK;
+}
+
 int bt_measure_h2d(int device, uint64_t nbytes, int iters, double* gb_per_s) {
   if (!gb_per_s || nbytes == 0 || iters < 1) return bt::fail(BT_E_INVALID, "bt_measure_h2d: bad arguments");
   BT_CUDA_TRY(cudaSetDevice(device));

@@ -403,3 +403,39 @@ def test_stream_raw_parts_wire(transport, receivers):
         for p in procs:
             p.terminate()
             p.join(timeout=10)
+
+
+@pytest.mark.parametrize("shuffle,drop_last", [(False, False), (True, True)])
+def test_pinned_host_recording_serves_every_epoch_identically(golden_dir, shuffle, drop_last):
+    """cache='host': the recording is read into page-locked memory once and every batch is gathered to
+    the device by DMA (bt_gather_h2d) -- same batches, bit for bit, as the uncached loader."""
+    ds = btt.FileDataset(str(golden_dir / "rec_small"))
+    kw = dict(batch_size=4, device=DEV, shuffle=shuffle, drop_last=drop_last, seed=7, keep_raw=True,
+              preprocess=btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5, stats=True))
+    plain, cached = btt.DeviceLoader(ds, **kw), btt.DeviceLoader(ds, cache="host", **kw)
+    want, got = _epochs(plain, 3), _epochs(cached, 3)
+    for e in range(3):
+        _same_batches(want[e], got[e])
+    assert cached.stats["cache_bytes"] > 0 and cached.stats["cache_fill_s"] > 0
+    assert cached.stats["bytes_h2d"] == plain.stats["bytes_h2d"]      # every epoch crosses PCIe, none touches the file
+    plain.close()
+    cached.close()
+    small = btt.DeviceLoader(ds, cache="host", cache_bytes=100, **kw)
+    with pytest.warns(UserWarning, match="replaying uncached"):
+        first = _epochs(small, 1)
+    _same_batches(want[0], first[0])
+    small.close()
+
+
+def test_gather_h2d_merges_runs_and_rejects_bad_rows():
+    import ctypes as C
+    from blendtorch.btt import native as N
+    src = torch.arange(64 * 37, dtype=torch.int32).reshape(64, 37).pin_memory()
+    idx = np.array([5, 6, 7, 0, 63, 62, 10, 11], dtype=np.int64)
+    dst = torch.empty((len(idx), 37), dtype=torch.int32, device=DEV)
+    st = torch.cuda.current_stream()
+    N.check(N.lib.bt_gather_h2d(dst.data_ptr(), src.data_ptr(), 37 * 4, idx.ctypes.data, len(idx), C.c_void_p(st.cuda_stream)))
+    st.synchronize()
+    assert torch.equal(dst.cpu(), src[torch.from_numpy(idx)])
+    bad = np.array([1, -2], dtype=np.int64)
+    assert N.lib.bt_gather_h2d(dst.data_ptr(), src.data_ptr(), 37 * 4, bad.ctypes.data, 2, C.c_void_p(st.cuda_stream)) == N.BT_E_INVALID

@@ -45,16 +45,20 @@ def case(name, config, h, w, batch, files, frames, spec, epochs=4):
         S.write_recordings(prefix, config, files, frames, h, w, pool=min(frames, 32))
         ds = btt.FileDataset(prefix)
         out = {"case": name, "frames": [h, w], "batch": batch, "items": len(ds)}
-        for mode in (None, "device"):
+        for mode in (None, "host", "device"):
             dl = btt.DeviceLoader(ds, batch_size=batch, shuffle=True, device=DEV, preprocess=spec, ingest_threads=4,
                                   ring_depth=3, prefetch=3, drop_last=False, cache=mode)
             rates = []
             for e in range(epochs):
                 n, wall, dev = epoch(dl)
                 rates.append({"images_per_s": round(n / wall, 1), "device_s": round(dev, 5), "wall_s": round(wall, 5)})
-            key = "resident" if mode else "uncached"
+            key = {None: "uncached", "host": "pinned_host", "device": "resident"}[mode]
             out[key] = rates
-            if mode:
+            if mode == "host":
+                out["host_cache_fill_s"] = round(dl.stats.get("cache_fill_s", 0), 3)
+                best = max(r["images_per_s"] for r in rates[1:])
+                out["pinned_host_GBps_h2d"] = round(best * os.path.getsize(ds.filenames[0]) / frames / 1e9, 1)
+            if mode == "device":
                 out["cache_bytes"] = dl.stats["cache_bytes"]
                 out["resident_batches"] = dl.stats["resident_batches"]
                 px_bytes = 4 + 4 * (4 if spec.dtype == torch.float32 else 2)
