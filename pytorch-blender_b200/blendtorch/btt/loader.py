@@ -152,7 +152,7 @@ class _Stager:
         batch = {}
         raw = torch.empty(max(used, 1), dtype=torch.uint8, device=self.device)
         if used and fill is not None:
-            fill(raw.data_ptr(), self._stream_handle)      # e.g. rows gathered from a pinned recording
+            fill(raw, self._stream_handle)      # e.g. rows gathered from a pinned recording
         elif used:
             self.ring.submit_batch(slot, sch, n, raw.data_ptr(), self._stream_handle)
         keep = [raw]                       # distinct storages the consumer stream must know about
@@ -196,8 +196,8 @@ class _HostCache:
     CPU copy per byte, on the worker pool); after that every batch of every epoch is assembled on the
     device by DMA (`bt_gather_h2d`): no file access, no scan, no CPU copy."""
 
-    def __init__(self, first_msg, n):
-        self.n = n
+    def __init__(self, first_msg, n, device):
+        self.n, self.device, self.small = n, device, {}
         self.schema = Schema.from_message(first_msg, n)
         if not self.schema.native or self.schema.host_keys:
             self.schema.close()
@@ -225,13 +225,31 @@ class _HostCache:
                 if self.schema.ingest_many(self.ptr, base + c0, addrs, lens, threads) >= 0:
                     return False
             base += count
+        # annotation columns (a few bytes per item) are also kept on the device, whole
+        view = self.mem.numpy()
+        for c in self.schema.columns:
+            if c.item_bytes < self.kSmall:
+                rows = view[c.slot_off:c.slot_off + self.n * c.item_bytes].view(c.dtype).reshape((self.n,) + tuple(c.shape))
+                self.small[c.key] = torch.from_numpy(rows).to(self.device)
         return True
 
-    def gather(self, plan, idx, raw_ptr, stream_handle):
-        """Rows `idx` of every column to the device batch at raw_ptr (the batch layout of `plan`)."""
+    kSmall = 16 * 1024   # columns with smaller items also live on the device (see `fill`)
+
+    def gather(self, plan, idx, raw, stream_handle, order_dev=None, start=0):
+        """Rows `idx` of every column to the device batch `raw` (the batch layout of `plan`): frames by
+        DMA from the page-locked recording, small annotation columns by an index_select from their
+        device copy (a DMA per 8-byte item would cost more than it moves)."""
         idx = np.ascontiguousarray(idx, dtype=np.int64)
-        for col, (_, off, ib, _, _, _) in zip(self.schema.columns, plan):
-            N.check(N.lib.bt_gather_h2d(raw_ptr + off, self.ptr + col.slot_off, ib, idx.ctypes.data, len(idx), stream_handle))
+        n = len(idx)
+        where = None
+        for col, (key, off, ib, dt, shape, _) in zip(self.schema.columns, plan):
+            small = self.small.get(key)
+            if small is not None:
+                if where is None:
+                    where = order_dev[start:start + n] if order_dev is not None else torch.from_numpy(idx).to(raw.device)
+                torch.index_select(small, 0, where, out=raw[off:off + n * ib].view(dt).view((n,) + tuple(shape)))
+            else:
+                N.check(N.lib.bt_gather_h2d(raw.data_ptr() + off, self.ptr + col.slot_off, ib, idx.ctypes.data, n, stream_handle))
 
     def close(self):
         self.schema.close()
@@ -435,7 +453,7 @@ class DeviceLoader:
                 budget = psutil.virtual_memory().available // 2
             if need > budget:
                 raise ValueError("recording needs %d bytes of page-locked memory, cache budget is %d" % (need, budget))
-            host = _HostCache(first, n)
+            host = _HostCache(first, n, self.device)
             if not host.fill(ds, max(self.ingest_threads, 1)):
                 host.close()
                 raise ValueError("a message needs the Python decode")
@@ -663,9 +681,10 @@ class DeviceLoader:
                     # the recording is in page-locked memory: this batch is a handful of DMA copies
                     if stager is None:
                         stager = self._new_stager(readers[0].raw(0), rid, depth=0)
+                        order_dev = torch.from_numpy(np.ascontiguousarray(order, dtype=np.int64)).to(self.device)
                     host, plan = self._host, stager.plan
                     if not self._emit(out_q, stop, stager, None, len(idx), {}, None, None,
-                                      lambda ptr, st, idx=idx: host.gather(plan, idx, ptr, st)):
+                                      lambda raw, st, idx=idx, start=start: host.gather(plan, idx, raw, st, order_dev, start)):
                         return
                     continue
                 fidx = np.searchsorted(cum, idx, side="right")
