@@ -129,6 +129,9 @@ def main():
                                           preprocess=btt.Preprocess(flip=True, gamma=GAMMA, mean=127.5, std=127.5))
                     res = train(model, opt, (b["image"] for b in dl), a.steps, a.warmup, dev)
                     res["h2d_GB_per_s"] = round(res["images_per_s"] * H * W * 4 / 1e9, 2)
+                    # who waited for whom: the training loop for data, or the receivers for room in the queue
+                    res["consumer_wait_s"] = round(dl.stats["consumer_wait_s"], 3)
+                    res["producer_wait_s"] = round(dl.stats["producer_wait_s"], 3)
                 else:
                     w = max(a.workers, 1)
                     per = (-(-total // w) + 2) * BATCH

@@ -23,6 +23,7 @@ goes through the pipeline above and leaves the *raw* columns (uint8 frames, 1/4 
 on the device; later epochs never touch the file, the host or PCIe -- the sampler's indices go to K1,
 which gathers its frames straight from the resident set.
 """
+import logging
 import pickle
 import queue
 import threading
@@ -44,6 +45,7 @@ from .rx import DirectReceiver, Receiver, direct_capable
 from .staging import Ring, Schema
 
 _DONE = object()
+_log = logging.getLogger("blendtorch")      # the reference's logger name (file.py:8)
 
 
 def shard(seq, rank, world_size):
@@ -335,8 +337,10 @@ class DeviceLoader:
         self.cache_mode, self.cache_bytes = cache, cache_bytes
         self._cache, self._cache_off, self._cache_lock = None, False, threading.Lock()
         self._host = None
+        # counters: who waits for whom tells which side is the bottleneck (consumer_wait_s: the training loop
+        # waited for a batch; producer_wait_s: receivers waited for room in the prefetch queue)
         self.stats = {"batches": 0, "items": 0, "bytes_h2d": 0, "kernels": 0, "compat_items": 0,
-                      "resident_batches": 0, "cache_bytes": 0}
+                      "resident_batches": 0, "cache_bytes": 0, "consumer_wait_s": 0.0, "producer_wait_s": 0.0}
         if isinstance(dataset, RemoteIterableDataset):
             if shuffle:
                 raise ValueError("iterable datasets do not support shuffle")
@@ -468,13 +472,17 @@ class DeviceLoader:
     def _emit(self, out_q, stop, stager, slot, n, host_rows, cache=None, idx=None, fill=None):
         item = stager.finish(slot, n, host_rows, cache, idx, fill)
         self.stats["bytes_h2d"] += stager.item_bytes * n
-        while not stop.is_set():
-            try:
-                out_q.put(item, timeout=0.1)
-                return True
-            except queue.Full:
-                continue
-        return False
+        t0 = time.perf_counter()
+        try:
+            while not stop.is_set():
+                try:
+                    out_q.put(item, timeout=0.1)
+                    return True
+                except queue.Full:
+                    continue
+            return False
+        finally:
+            self.stats["producer_wait_s"] += time.perf_counter() - t0
 
     def _stream_producer(self, rid, out_q, stop):
         ds = self.dataset
@@ -815,12 +823,14 @@ class DeviceLoader:
         turn = 0
         try:
             while any(alive):
+                t0 = time.perf_counter()
                 if ordered:
                     if not alive[turn]:
                         break                      # the producer whose turn it is has no more batches
                     item = queues[turn].get()
                 else:
                     item = queues[0].get()
+                self.stats["consumer_wait_s"] += time.perf_counter() - t0
                 if item is _DONE:
                     if ordered:
                         alive[turn] = False
@@ -848,6 +858,7 @@ class DeviceLoader:
                     turn = (turn + 1) % n_prod
         finally:
             stop.set()
+            _log.debug("DeviceLoader epoch %d: %s", self._epoch, self.stats)
             # unblock producers waiting on a full queue, then let them finish cleanly
             for t, q in zip(threads, queues):
                 while t.is_alive():
