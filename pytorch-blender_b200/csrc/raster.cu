@@ -20,7 +20,9 @@
 
 namespace {
 
-constexpr int kTile = 16;
+constexpr int kTile = 16;     // pixels per side of a tile: one pixel per thread
+constexpr int kRegion = 4;    // tiles per side of the region a CTA rasterises: the projection and triangle
+                              // set-up below are done once per CTA, so they are shared by 16 tiles
 constexpr int kMaxCubes = 32;
 constexpr int kTrisPerCube = 12;
 
@@ -63,9 +65,12 @@ __global__ void __launch_bounds__(kTile* kTile) k3_raster(bt_raster_params p) {
   __shared__ float cx[kMaxCubes * 8], cy[kMaxCubes * 8], cz[kMaxCubes * 8];
   __shared__ unsigned char ok[kMaxCubes * 8];
   __shared__ Tri tris[kMaxCubes * kTrisPerCube];
+  __shared__ float bminx[kMaxCubes * kTrisPerCube], bmaxx[kMaxCubes * kTrisPerCube];
+  __shared__ float bminy[kMaxCubes * kTrisPerCube], bmaxy[kMaxCubes * kTrisPerCube];
   __shared__ unsigned char live[kMaxCubes * kTrisPerCube];
-  __shared__ unsigned short order[kMaxCubes * kTrisPerCube];
-  __shared__ int nlive;
+  __shared__ unsigned short region_order[kMaxCubes * kTrisPerCube];   // triangles that can touch the region
+  __shared__ unsigned short order[kMaxCubes * kTrisPerCube];          // ... and the current tile
+  __shared__ int nregion, nlive;
 
   const int b = blockIdx.z;
   const int tid = threadIdx.y * kTile + threadIdx.x;
@@ -98,8 +103,8 @@ __global__ void __launch_bounds__(kTile* kTile) k3_raster(bt_raster_params p) {
 
   // phase B: triangle set-up, tile culling, flat shading (one thread per triangle; live[t] says
   // whether triangle t can touch this tile at all)
-  const float tx0 = (float)(blockIdx.x * kTile), ty0 = (float)(blockIdx.y * kTile);
-  const float tx1 = tx0 + (float)kTile, ty1 = ty0 + (float)kTile;
+  const float rx0 = (float)(blockIdx.x * kTile * kRegion), ry0 = (float)(blockIdx.y * kTile * kRegion);
+  const float rx1 = rx0 + (float)(kTile * kRegion), ry1 = ry0 + (float)(kTile * kRegion);
   const float ll = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(p.light[0], p.light[0]), __fmul_rn(p.light[1], p.light[1])),
                                         __fmul_rn(p.light[2], p.light[2])));
   for (int t = tid; t < p.ncubes * kTrisPerCube; t += kTile * kTile) {
@@ -113,7 +118,8 @@ __global__ void __launch_bounds__(kTile* kTile) k3_raster(bt_raster_params p) {
     if (tr.area == 0.0f) continue;
     const float minx = fminf(tr.x0, fminf(tr.x1, tr.x2)), maxx = fmaxf(tr.x0, fmaxf(tr.x1, tr.x2));
     const float miny = fminf(tr.y0, fminf(tr.y1, tr.y2)), maxy = fmaxf(tr.y0, fmaxf(tr.y1, tr.y2));
-    if (maxx < tx0 || minx > tx1 || maxy < ty0 || miny > ty1) continue;  // conservative: cannot touch this tile
+    if (maxx < rx0 || minx > rx1 || maxy < ry0 || miny > ry1) continue;  // conservative: cannot touch this region
+    bminx[t] = minx; bmaxx[t] = maxx; bminy[t] = miny; bmaxy[t] = maxy;
     if (perspective) {
       tr.q0 = __fdiv_rn(1.0f, sd[i0]); tr.q1 = __fdiv_rn(1.0f, sd[i1]); tr.q2 = __fdiv_rn(1.0f, sd[i2]);
     } else {
@@ -144,7 +150,7 @@ __global__ void __launch_bounds__(kTile* kTile) k3_raster(bt_raster_params p) {
     live[t] = 1;
   }
   __syncthreads();
-  // order-preserving compaction of the triangles that can touch this tile (most tiles see a few
+  // order-preserving compaction of the triangles that can touch this region (most regions see a few
   // of the 12*ncubes): warp 0 scans the flags 32 at a time with ballots
   if (tid < 32) {
     int base = 0;
@@ -152,39 +158,65 @@ __global__ void __launch_bounds__(kTile* kTile) k3_raster(bt_raster_params p) {
       const int t = t0 + tid;
       const bool on = t < p.ncubes * kTrisPerCube && live[t];
       const unsigned m = __ballot_sync(0xffffffffu, on);
-      if (on) order[base + __popc(m & ((1u << tid) - 1u))] = (unsigned short)t;
+      if (on) region_order[base + __popc(m & ((1u << tid) - 1u))] = (unsigned short)t;
       base += __popc(m);
     }
-    if (tid == 0) nlive = base;
+    if (tid == 0) nregion = base;
   }
   __syncthreads();
 
-  // phase C: one pixel per thread, nearest depth wins; ties keep the lower triangle index
-  const int px = blockIdx.x * kTile + threadIdx.x, py = blockIdx.y * kTile + threadIdx.y;
-  if (px >= p.width || py >= p.height) return;
-  const float fx = (float)px + 0.5f, fy = (float)py + 0.5f;
-  float best = FLT_MAX;
-  unsigned int color = (unsigned int)p.background[0] | ((unsigned int)p.background[1] << 8) |
-                       ((unsigned int)p.background[2] << 16) | ((unsigned int)p.background[3] << 24);
-  {
-    for (int j = 0; j < nlive; ++j) {
-      const Tri& tr = tris[order[j]];
-      float w0 = edge(tr.x1, tr.y1, tr.x2, tr.y2, fx, fy);
-      float w1 = edge(tr.x2, tr.y2, tr.x0, tr.y0, fx, fy);
-      float w2 = edge(tr.x0, tr.y0, tr.x1, tr.y1, fx, fy);
-      if (tr.area < 0.0f) { w0 = -w0; w1 = -w1; w2 = -w2; }
-      if (w0 < 0.0f || w1 < 0.0f || w2 < 0.0f) continue;
-      const float aa = fabsf(tr.area);
-      const float b0 = __fdiv_rn(w0, aa), b1 = __fdiv_rn(w1, aa), b2 = __fdiv_rn(w2, aa);
-      float q = __fadd_rn(__fadd_rn(__fmul_rn(b0, tr.q0), __fmul_rn(b1, tr.q1)), __fmul_rn(b2, tr.q2));
-      const float d = perspective ? __fdiv_rn(1.0f, q) : q;
-      if (d < best) { best = d; color = tr.rgba; }
+  const unsigned int background = (unsigned int)p.background[0] | ((unsigned int)p.background[1] << 8) |
+                                  ((unsigned int)p.background[2] << 16) | ((unsigned int)p.background[3] << 24);
+  for (int tile = 0; tile < kRegion * kRegion; ++tile) {
+    const int tile_x = blockIdx.x * kRegion + (tile % kRegion), tile_y = blockIdx.y * kRegion + (tile / kRegion);
+    if (tile_x * kTile >= p.width || tile_y * kTile >= p.height) continue;   // (uniform: the whole CTA skips)
+    // the region's triangles that can touch this tile, same order, same conservative test
+    const float tx0 = (float)(tile_x * kTile), ty0 = (float)(tile_y * kTile);
+    const float tx1 = tx0 + (float)kTile, ty1 = ty0 + (float)kTile;
+    if (tid < 32) {
+      int base = 0;
+      for (int j0 = 0; j0 < nregion; j0 += 32) {
+        const int j = j0 + tid;
+        bool on = false;
+        unsigned short t = 0;
+        if (j < nregion) {
+          t = region_order[j];
+          on = !(bmaxx[t] < tx0 || bminx[t] > tx1 || bmaxy[t] < ty0 || bminy[t] > ty1);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, on);
+        if (on) order[base + __popc(m & ((1u << tid) - 1u))] = t;
+        base += __popc(m);
+      }
+      if (tid == 0) nlive = base;
     }
+    __syncthreads();
+
+    // phase C: one pixel per thread, nearest depth wins; ties keep the lower triangle index
+    const int px = tile_x * kTile + threadIdx.x, py = tile_y * kTile + threadIdx.y;
+    if (px < p.width && py < p.height) {
+      const float fx = (float)px + 0.5f, fy = (float)py + 0.5f;
+      float best = FLT_MAX;
+      unsigned int color = background;
+      for (int j = 0; j < nlive; ++j) {
+        const Tri& tr = tris[order[j]];
+        float w0 = edge(tr.x1, tr.y1, tr.x2, tr.y2, fx, fy);
+        float w1 = edge(tr.x2, tr.y2, tr.x0, tr.y0, fx, fy);
+        float w2 = edge(tr.x0, tr.y0, tr.x1, tr.y1, fx, fy);
+        if (tr.area < 0.0f) { w0 = -w0; w1 = -w1; w2 = -w2; }
+        if (w0 < 0.0f || w1 < 0.0f || w2 < 0.0f) continue;
+        const float aa = fabsf(tr.area);
+        const float b0 = __fdiv_rn(w0, aa), b1 = __fdiv_rn(w1, aa), b2 = __fdiv_rn(w2, aa);
+        float q = __fadd_rn(__fadd_rn(__fmul_rn(b0, tr.q0), __fmul_rn(b1, tr.q1)), __fmul_rn(b2, tr.q2));
+        const float d = perspective ? __fdiv_rn(1.0f, q) : q;
+        if (d < best) { best = d; color = tr.rgba; }
+      }
+      const int row = p.bottom_up ? p.height - 1 - py : py;
+      const size_t o = ((size_t)b * p.height + row) * p.width + px;
+      reinterpret_cast<unsigned int*>(p.image_out)[o] = color;
+      if (p.depth_out) p.depth_out[o] = best == FLT_MAX ? p.far_depth : best;
+    }
+    __syncthreads();   // the tile list is rewritten for the next tile
   }
-  const int row = p.bottom_up ? p.height - 1 - py : py;
-  const size_t o = ((size_t)b * p.height + row) * p.width + px;
-  reinterpret_cast<unsigned int*>(p.image_out)[o] = color;
-  if (p.depth_out) p.depth_out[o] = best == FLT_MAX ? p.far_depth : best;
 }
 
 }  // namespace
@@ -197,7 +229,8 @@ extern "C" int bt_raster_launch(const bt_raster_params* p, void* stream) {
   if (reinterpret_cast<uintptr_t>(p->image_out) % 4) return bt::fail(BT_E_INVALID, "image_out must be 4-byte aligned");
   if (p->batch == 0) return BT_OK;
   if (p->batch > 65535) return bt::fail(BT_E_TOO_LARGE, "at most 65535 frames per launch");
-  dim3 grid((p->width + kTile - 1) / kTile, (p->height + kTile - 1) / kTile, p->batch);
+  constexpr int kSide = kTile * kRegion;
+  dim3 grid((p->width + kSide - 1) / kSide, (p->height + kSide - 1) / kSide, p->batch);
   k3_raster<<<grid, dim3(kTile, kTile), 0, static_cast<cudaStream_t>(stream)>>>(*p);
   BT_CUDA_TRY(cudaGetLastError());
   return BT_OK;
