@@ -21,8 +21,9 @@
 namespace {
 
 constexpr int kTile = 16;     // pixels per side of a tile: one pixel per thread
-constexpr int kRegion = 4;    // tiles per side of the region a CTA rasterises: the projection and triangle
-                              // set-up below are done once per CTA, so they are shared by 16 tiles
+// kRegion (template parameter): tiles per side of the region a CTA rasterises.  The projection and triangle
+// set-up below are done once per CTA, so a 4x4 region shares them between 16 tiles; small batches use 2x2
+// regions to keep enough CTAs in flight.
 constexpr int kMaxCubes = 32;
 constexpr int kTrisPerCube = 12;
 
@@ -60,6 +61,7 @@ __device__ __forceinline__ float edge(float ax, float ay, float bx, float by, fl
   return __fsub_rn(__fmul_rn(__fsub_rn(bx, ax), __fsub_rn(py, ay)), __fmul_rn(__fsub_rn(by, ay), __fsub_rn(px, ax)));
 }
 
+template <int kRegion>
 __global__ void __launch_bounds__(kTile* kTile) k3_raster(bt_raster_params p) {
   __shared__ float sx[kMaxCubes * 8], sy[kMaxCubes * 8], sd[kMaxCubes * 8];
   __shared__ float cx[kMaxCubes * 8], cy[kMaxCubes * 8], cz[kMaxCubes * 8];
@@ -229,9 +231,17 @@ extern "C" int bt_raster_launch(const bt_raster_params* p, void* stream) {
   if (reinterpret_cast<uintptr_t>(p->image_out) % 4) return bt::fail(BT_E_INVALID, "image_out must be 4-byte aligned");
   if (p->batch == 0) return BT_OK;
   if (p->batch > 65535) return bt::fail(BT_E_TOO_LARGE, "at most 65535 frames per launch");
-  constexpr int kSide = kTile * kRegion;
-  dim3 grid((p->width + kSide - 1) / kSide, (p->height + kSide - 1) / kSide, p->batch);
-  k3_raster<<<grid, dim3(kTile, kTile), 0, static_cast<cudaStream_t>(stream)>>>(*p);
+  auto regions = [&](int side) { return (uint64_t)((p->width + side - 1) / side) * ((p->height + side - 1) / side) * p->batch; };
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (regions(kTile * 4) >= 2048) {   // enough 64x64 regions to fill the GPU several times over
+    constexpr int kSide = kTile * 4;
+    dim3 grid((p->width + kSide - 1) / kSide, (p->height + kSide - 1) / kSide, p->batch);
+    k3_raster<4><<<grid, dim3(kTile, kTile), 0, st>>>(*p);
+  } else {
+    constexpr int kSide = kTile * 2;
+    dim3 grid((p->width + kSide - 1) / kSide, (p->height + kSide - 1) / kSide, p->batch);
+    k3_raster<2><<<grid, dim3(kTile, kTile), 0, st>>>(*p);
+  }
   BT_CUDA_TRY(cudaGetLastError());
   return BT_OK;
 }
