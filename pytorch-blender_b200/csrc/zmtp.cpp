@@ -75,6 +75,9 @@ struct External {
   const uint8_t* where;
 };
 
+// diagnostic counters (printed at bt_pull_destroy when BT_RX_STATS is set)
+thread_local uint64_t g_recv_calls = 0, g_poll_calls = 0;
+
 constexpr int kIoTimeoutMs = 10000;  // a message that started arriving must complete within this
 
 void close_peer(Peer& p) {
@@ -91,6 +94,7 @@ int read_exact(int fd, uint8_t* dst, uint64_t n, int timeout_ms) {
   const uint64_t deadline = now_ms() + (uint64_t)timeout_ms;
   while (n) {
     ssize_t k = recv(fd, dst, n > (1u << 30) ? (1u << 30) : (size_t)n, 0);
+    ++g_recv_calls;
     if (k > 0) { dst += k; n -= (uint64_t)k; continue; }
     if (k == 0) return bt::fail(BT_E_IO, "peer closed the connection");
     if (errno == EINTR) continue;
@@ -99,6 +103,7 @@ int read_exact(int fd, uint8_t* dst, uint64_t n, int timeout_ms) {
     if (now >= deadline) return bt::fail(BT_E_IO, "peer stalled in the middle of a message");
     pollfd pf = {fd, POLLIN, 0};
     poll(&pf, 1, (int)(deadline - now));
+    ++g_poll_calls;
   }
   return BT_OK;
 }
@@ -649,6 +654,10 @@ int bt_pull_connect(bt_pull* q, const char* address) {
 
 int bt_pull_destroy(bt_pull* q) {
   if (!q) return BT_OK;
+  if (getenv("BT_RX_STATS") && q->messages)
+    fprintf(stderr, "bt_pull: %llu messages, %.1f MB each, %.1f recv and %.1f poll calls per message (payload reads)\n",
+            (unsigned long long)q->messages, (double)q->bytes / q->messages / 1e6, (double)g_recv_calls / q->messages,
+            (double)g_poll_calls / q->messages);
   for (Peer& p : q->peers)
     if (p.fd >= 0) close(p.fd);
   delete q;
