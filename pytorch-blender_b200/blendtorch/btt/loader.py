@@ -42,7 +42,7 @@ from .dataset import FileDataset, RemoteIterableDataset, open_pull_socket
 from .file import FileRecorder
 from .preprocess import PreparedPreprocess, Preprocess
 from .rx import DirectReceiver, Receiver, direct_capable
-from .staging import Ring, Schema
+from .staging import Ring, Schema, refuse_pickle
 
 _DONE = object()
 _log = logging.getLogger("blendtorch")      # the reference's logger name (file.py:8)
@@ -284,6 +284,10 @@ class DeviceLoader:
         spread over them, so socket reads of different publishers proceed in parallel.
     seed: shuffle seed (epoch number is added on every new iteration).
     keep_raw: also return the untouched uint8 frames as ``<key>_raw``.
+    allow_pickle: False = never unpickle.  The reference unpickles every message it receives
+        (dataset.py:103,105), and unpickling data from a socket can run code; the native scanner only
+        locates payloads.  With False, a message outside its subset raises instead of being decoded by
+        ``pickle.loads`` (so no item_transform, no recording tee, no string fields).
     cache: 'device' keeps a replayed recording resident in HBM (raw columns, i.e. uint8 frames): the
         first epoch fills it on the way through, every later epoch is served from it -- no file, host
         or PCIe traffic; K1 gathers the sampler's frames straight from the resident set.  Only for
@@ -299,7 +303,7 @@ class DeviceLoader:
     def __init__(self, dataset, batch_size=1, shuffle=False, drop_last=False, device="cuda",
                  preprocess=None, num_receivers=None, ring_depth=3, prefetch=2, ingest_threads=4,
                  seed=0, keep_raw=False, io_threads=1, project=None, transport="auto", cache=None,
-                 cache_bytes=None):
+                 cache_bytes=None, allow_pickle=True):
         self.dataset = dataset
         self.batch_size = int(batch_size)
         if self.batch_size < 1:
@@ -349,6 +353,9 @@ class DeviceLoader:
             self._mode = "replay"
         else:
             raise TypeError("DeviceLoader takes a btt.RemoteIterableDataset or a btt.FileDataset")
+        self.allow_pickle = bool(allow_pickle)
+        if not self.allow_pickle and (dataset.has_custom_item() or getattr(dataset, "record_path_prefix", None)):
+            raise ValueError("allow_pickle=False excludes item transforms and the recording tee (both need unpickled items)")
         if cache is not None and (self._mode != "replay" or dataset.has_custom_item()):
             raise ValueError("cache=%r is for FileDataset replay without an item_transform" % cache)
 
@@ -367,7 +374,7 @@ class DeviceLoader:
         """Stager for the stream that starts with `first_msg`.  Pinned rings are expensive to create
         (page-locking hundreds of MB takes longer than an epoch of small recordings), so a stager
         is kept per producer and reused by later epochs while the layout stays the same."""
-        schema = Schema.from_message(first_msg, self.batch_size, sizes)
+        schema = Schema.from_message(first_msg, self.batch_size, sizes, self.allow_pickle)
         for key in self.specs:
             c = schema.column(key)  # KeyError: the named image field is not in the messages
             if c.dtype != np.uint8:
@@ -532,10 +539,10 @@ class DeviceLoader:
             self._retire(stager)
             out_q.put(_DONE)
 
-    @staticmethod
-    def _decode_pending(rx):
+    def _decode_pending(self, rx):
         """The held message as the object the producer published (the reference's decode, for either
         framing): raw-parts frames are joined, shared-memory references fetched."""
+        refuse_pickle(self.allow_pickle)
         msg, sizes = rx.pending(), rx.pending_parts()
         if len(sizes) > 1:
             obj = wire.loads(msg, sizes)

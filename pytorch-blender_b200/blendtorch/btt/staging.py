@@ -36,6 +36,14 @@ class ColumnSpec:
         return "ColumnSpec(%r, %s%s @%d)" % (self.key, self.dtype, list(self.shape), self.slot_off)
 
 
+def refuse_pickle(allow_pickle):
+    """The reference unpickles whatever arrives on the socket (dataset.py:103,105); pickle can run code.
+    The native scanner never does; with allow_pickle=False nothing else is allowed to decode a message."""
+    if not allow_pickle:
+        raise RuntimeError("message outside the natively scanned subset (%s) and allow_pickle=False"
+                           % (N.last_error() or "no reason recorded"))
+
+
 def _align(v):
     return (v + _ALIGN - 1) // _ALIGN * _ALIGN
 
@@ -48,6 +56,7 @@ class Schema:
         self.columns = columns
         self.host_keys = tuple(host_keys)  # fields kept on the host (str etc.), collated as lists
         self.handle = handle               # bt_schema* when the native fast path applies
+        self.allow_pickle = True           # False: refuse messages that would need pickle.loads
         end = 0
         for c in columns:
             end = max(end, c.slot_off + c.item_bytes * batch)
@@ -58,9 +67,10 @@ class Schema:
         return self.handle is not None
 
     @classmethod
-    def from_message(cls, msg, batch, sizes=None):
+    def from_message(cls, msg, batch, sizes=None, allow_pickle=True):
         """Derive the schema from the first message of a stream (bytes-like pickle).  `sizes`: frame
-        sizes when `msg` holds a raw-parts message (wire.py), header frame first."""
+        sizes when `msg` holds a raw-parts message (wire.py), header frame first.  `allow_pickle=False`:
+        messages the native scanner does not cover are refused instead of unpickled."""
         addr, n = N.buffer_address(msg)
         if sizes is not None and len(sizes) > 1:
             n = int(sizes[0])
@@ -73,9 +83,12 @@ class Schema:
                 N.check(N.lib.bt_schema_column(h, i, C.byref(col)))
                 cols.append(ColumnSpec(col.key.decode(), col.kind, N.NUMPY_DTYPES[col.dtype],
                                        [col.shape[d] for d in range(col.ndim)], col.item_bytes, col.slot_off))
-            return cls(batch, cols, handle=h)
+            out = cls(batch, cols, handle=h)
+            out.allow_pickle = allow_pickle
+            return out
         if rc not in (N.BT_E_UNSUPPORTED,):
             N.check(rc)
+        refuse_pickle(allow_pickle)
         return cls.from_object(shm.resolve(wire.loads(msg, sizes)), batch)
 
     @classmethod
@@ -134,6 +147,7 @@ class Schema:
                 return
             if rc not in (N.BT_E_UNSUPPORTED, N.BT_E_SCHEMA):
                 N.check(rc)
+        refuse_pickle(self.allow_pickle)
         self.ingest_object(slot_view, item, shm.resolve(pickle.loads(msg)), host_rows)
 
     def ingest_object(self, slot_view, item, obj, host_rows=None):
@@ -211,6 +225,7 @@ class Ring:
                 return
             if rc not in (N.BT_E_UNSUPPORTED, N.BT_E_SCHEMA):
                 N.check(rc)
+        refuse_pickle(schema.allow_pickle)
         schema.ingest_object(self._views[slot], item, shm.resolve(pickle.loads(msg)), host_rows)
 
     def submit_batch(self, slot, schema, n_items, dev_ptr, stream_handle):

@@ -439,3 +439,31 @@ def test_gather_h2d_merges_runs_and_rejects_bad_rows():
     assert torch.equal(dst.cpu(), src[torch.from_numpy(idx)])
     bad = np.array([1, -2], dtype=np.int64)
     assert N.lib.bt_gather_h2d(dst.data_ptr(), src.data_ptr(), 37 * 4, bad.ctypes.data, 2, C.c_void_p(st.cuda_stream)) == N.BT_E_INVALID
+
+
+def test_allow_pickle_false_never_unpickles():
+    """The reference unpickles whatever arrives (dataset.py:103,105).  With allow_pickle=False ordinary
+    streams run entirely on the scanner; a message that would need pickle.loads raises instead."""
+    def pub(addr, with_string):
+        with btt.DataPublisher(addr, 3, lingerms=10000) as p:
+            for i in range(4):
+                extra = {"name": "n%d" % i} if with_string else {}
+                p.publish(image=np.full((8, 16, 4), i, np.uint8), frameid=i, **extra)
+    for with_string in (False, True):
+        addr = "tcp://127.0.0.1:%d" % _free_port()
+        pr = mp.get_context("fork").Process(target=pub, args=(addr, with_string), daemon=True)
+        pr.start()
+        try:
+            ds = btt.RemoteIterableDataset([addr], max_items=4)
+            dl = btt.DeviceLoader(ds, batch_size=2, device=DEV, allow_pickle=False)
+            if with_string:
+                with pytest.raises(RuntimeError, match="allow_pickle=False"):
+                    list(dl)
+            else:
+                bs = list(dl)
+                assert [b["frameid"].tolist() for b in bs] == [[0, 1], [2, 3]] and dl.stats["compat_items"] == 0
+        finally:
+            pr.join(timeout=10)
+    with pytest.raises(ValueError, match="allow_pickle=False"):
+        btt.DeviceLoader(btt.RemoteIterableDataset(["tcp://127.0.0.1:1"], item_transform=lambda x: x), device=DEV,
+                         allow_pickle=False)
