@@ -9,7 +9,7 @@ This package restates, in plain numpy / stdlib pickle, what the reference
 so that the CUDA path can be compared against it byte for byte.  Each function
 cites the reference file:line it follows (paths relative to the reference root).
 
-Rules (enforced by tests/test_boundary_rules.py):
+Rules (enforced by tests/test_abi_and_rules.py):
   * only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
     --impl reference legs may import anything from here;
   * the product package (pytorch-blender_b200/) never imports it and has no CPU

@@ -8,6 +8,7 @@ are supplied by the caller (the bpy getters camera.py:57-82 have no place on the
 """
 import ctypes as C
 
+import numpy as np
 import torch
 
 from . import native as N
@@ -35,6 +36,31 @@ class Camera:
             if m.shape[-2:] != (4, 4) or m.dim() not in (2, 3):
                 raise ValueError("matrices must be (4,4) or (B,4,4)")
         self.shape = tuple(shape)
+
+    @classmethod
+    def from_lens(cls, shape, lens=50.0, sensor=36.0, near=0.1, far=100.0, distance=7.0, ortho_scale=None,
+                  device="cuda"):
+        """A camera without Blender: on the +Z axis at `distance`, looking at the origin, Y up, with the
+        projection Blender computes for a perspective camera of focal length `lens` on a `sensor` mm wide
+        sensor (horizontal fit) -- or an orthographic one of `ortho_scale`.  Stands in for the bpy-dependent
+        getters of the reference (btb/camera.py:57-82) in synthetic scenes, benchmarks and examples."""
+        h, w = shape
+        view = np.eye(4)
+        view[2, 3] = -float(distance)
+        proj = np.zeros((4, 4))
+        if ortho_scale is None:
+            proj[0, 0] = 2.0 * lens / sensor
+            proj[1, 1] = proj[0, 0] * w / h
+            proj[2, 2] = -(far + near) / (far - near)
+            proj[2, 3] = -2.0 * far * near / (far - near)
+            proj[3, 2] = -1.0
+        else:
+            proj[0, 0] = 2.0 / ortho_scale
+            proj[1, 1] = proj[0, 0] * w / h
+            proj[2, 2] = -2.0 / (far - near)
+            proj[2, 3] = -(far + near) / (far - near)
+            proj[3, 3] = 1.0
+        return cls(view, proj, shape, device=device)
 
     # -- internals ---------------------------------------------------------------------------
     def _points(self, xyz):

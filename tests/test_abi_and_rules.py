@@ -87,6 +87,13 @@ def test_device_paths_fail_loudly_without_cuda():
         btt.Camera(np.eye(4), np.eye(4), (4, 4), device="cpu")
 
 
+def test_only_tests_smoke_and_bench_touch_the_oracle():
+    """Diagnostic tools and examples use the product; the oracle is for tests, smoke() and bench.py's CPU legs."""
+    for folder in ("tools", "examples"):
+        for f in sorted((ROOT / folder).glob("*.py")):
+            assert not re.search(r"^\s*(from|import)\s+oracle\b", f.read_text(), flags=re.M), f
+
+
 def test_synthetic_generators_agree_with_oracle_copy():
     from blendtorch.btt import synthetic as S
     from oracle import synth as O

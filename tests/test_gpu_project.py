@@ -30,6 +30,14 @@ def test_reference_camera_goldens(golden_dir):
             px = cam.ndc_to_pixel(g["ref_%s_ndc" % tag], origin=origin)
             assert_allclose(px.cpu().numpy(), g["ref_%s_px_%s" % (tag, "ul" if origin[0] == "u" else "ll")],
                             rtol=RTOL, atol=1e-9)
+    # the bpy-free constructor gives the matrices of the reference's test scene (cam.blend: 50 mm lens on a
+    # 36 mm sensor at z = 7 looking down -Z; ortho_scale 4), hence the reference's own expected pixels
+    for cam, exp in ((btt.Camera.from_lens(shape), g["expected_proj_xy"]),
+                     (btt.Camera.from_lens(shape, ortho_scale=4.0), g["expected_ortho_xy"])):
+        np.testing.assert_array_equal(cam.view_matrix.cpu().numpy(), g["V"])
+        xy, z = cam.world_to_pixel(g["cube"], return_depth=True)
+        assert_allclose(xy.cpu().numpy(), exp, atol=1e-2)
+        assert_allclose(z.cpu().numpy(), g["expected_z"], atol=1e-2)
     cam = btt.Camera(g["rand_V"], g["rand_P"], (1080, 1920))
     xy, z = cam.world_to_pixel(g["rand_pts"], return_depth=True)
     assert_allclose(xy.cpu().numpy(), g["rand_px_ul"], rtol=1e-11, atol=1e-9)

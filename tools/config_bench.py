@@ -87,9 +87,8 @@ def main():
     out = []
     for th, pr in ((1, 1), (4, 1), (4, 2), (4, 3), (2, 4)):
         out.append(replay_case("C1 replay 640x480 b8 (.btr in page cache)", 1, 480, 640, 8, 4, 256, th, 400, spec, producers=pr))
-    from oracle import camera as ocam
     shape = (1080, 1920)
-    cam = btt.Camera(ocam.view_looking_down_z(0.0), ocam.blender_perspective(shape, lens=35.0), shape, device=DEV)
+    cam = btt.Camera.from_lens(shape, lens=35.0, distance=0.0, device=DEV)
 
     def project(b):
         b["xy"], b["boxes"] = cam.bbox_world_to_pixel_boxes(b["corners"], 8)

@@ -12,7 +12,6 @@ import torch  # noqa: E402
 
 from blendtorch import btt  # noqa: E402
 from blendtorch.btt import synthetic as S  # noqa: E402
-from oracle import camera as ocam  # noqa: E402  (matrices only)
 
 
 def main():
@@ -20,9 +19,9 @@ def main():
     spec = btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5)
     for (B, H, W) in ((8, 480, 640), (32, 1080, 1920), (64, 1024, 1024)):
         scenes = np.stack([S.cube_corners(S.rng_for(3, b)).reshape(8, 8, 3) for b in range(B)])
-        V, P = ocam.view_looking_down_z(20.0), ocam.blender_perspective((H, W), lens=35.0)
+        cam = btt.Camera.from_lens((H, W), lens=35.0, distance=20.0, device=dev)
         pts = torch.as_tensor(scenes, device=dev)
-        Vt, Pt = torch.as_tensor(V, device=dev), torch.as_tensor(P, device=dev)
+        Vt, Pt = cam.view_matrix, cam.proj_matrix
         res = {}
         for name, chain in (("k3", False), ("k3+k1", True)):
             for _ in range(3):
