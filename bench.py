@@ -475,7 +475,7 @@ def ours(args):
                          "traffic_note": "ncu, cold L2: 9.85 MB read (= algorithmic 9.83 MB) + <0.2 MB written back inside the "
                                          "kernel; the 39.3 MB of fp32 output of a batch-8 launch are absorbed by the 126 MB L2 "
                                          "and written back after it (C4-size launches write through: see profiles/)",
-                         "kernel": "k1_planar<float,4,4,4>", "algorithmic_bytes_per_launch": algo_bytes,
+                         "kernel": "k1_planar<float,4,4,1> (C,PPT,UNROLL: one 4-pixel unit per thread at this batch size)", "algorithmic_bytes_per_launch": algo_bytes,
                          "frac_of_nominal_8TBs": achieved / 8000.0,
                          "large_batch": {"workload": "C4 per-GPU batch: 64 x 1024x1024 RGBA -> fp32 NCHW",
                                          "achieved": large_gbs, "frac": large_gbs / peak, "ms": large_sec * 1e3}},

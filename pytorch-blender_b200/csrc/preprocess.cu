@@ -758,6 +758,10 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
         if (tune_unroll == 1) LAUNCH_PLANAR(4, 4, 1);
         if (tune_unroll == 2) LAUNCH_PLANAR(4, 4, 2);
         if (tune_unroll == 8) LAUNCH_PLANAR(4, 4, 8);
+        // One unit per thread (more, shorter CTAs) is 2-5 % faster up to batches of about 8 M units --
+        // batch 8..64 of 640x480, 1024 x 128^2 (0.97 vs 0.92 of peak) -- and 1 % slower beyond, where
+        // four units in flight per thread win (profiles/r1_k1_unroll.txt).
+        if (tune_unroll == 0 && rows * (a.W / 4) < (8u << 20)) LAUNCH_PLANAR(4, 4, 1);
       }
       LAUNCH_PLANAR(4, 4, 4);
     }

@@ -112,6 +112,12 @@ def main():
                   for n in ((1, 2, 4) if sh == C2 else (1,))]
         cases += [dict(shape=C2, dtype=torch.float32, variant=v, streams=n) for v in ("bulk",) for n in (1, 2, 4)]
         cases += [dict(shape=C4, dtype=torch.float32, variant="bulk")]
+    elif len(sys.argv) > 1 and sys.argv[1] == "unroll2":
+        cases = [dict(shape=sh, dtype=dt, tune=t) for sh in (C4, C3, C5, (256, 480, 640, 4))
+                 for dt in (torch.float32, torch.bfloat16) for t in ((0, 1, 2) if dt == torch.float32 else (0, 1, 4))] * 2
+    elif len(sys.argv) > 1 and sys.argv[1] == "unroll":
+        cases = [dict(shape=(b, 480, 640, 4), dtype=torch.float32, streams=n, tune=t) for b in (8, 16, 32, 64)
+                 for n in (1, 4, 8) for t in (0, 1, 2)] * 2
     elif len(sys.argv) > 1 and sys.argv[1] == "bulk":
         cases = []
         for shape in (C2, C4, C3, C5):
