@@ -575,13 +575,15 @@ __global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a, PlanarGeom 
 template <typename T, int C, bool CHW, int UNROLL, bool STATS>
 __global__ void __launch_bounds__(kThreads) k1_pixel(K1Args a, PlanarGeom g) {
   __shared__ T lut[kMaxC * 256];
-  build_lut<T>(a, lut);
+  const bool loads_first = (a.flags & 1u) != 0;   // as in k1_planar: the table build hides under the first loads
+  if (!loads_first) build_lut<T>(a, lut);
   StatAcc acc;
   if (STATS) acc.clear();
   const uint32_t plane = a.H * a.W;
   T* dst = static_cast<T*>(a.dst);
   const uint32_t stride = gridDim.x * blockDim.x;
-  for (uint32_t u0 = blockIdx.x * blockDim.x + threadIdx.x; u0 < g.total_units; u0 += stride * UNROLL) {
+  bool need_lut = loads_first;
+  for (uint32_t u0 = blockIdx.x * blockDim.x + threadIdx.x; need_lut || u0 < g.total_units; u0 += stride * UNROLL) {
     uint32_t px[UNROLL];
     uint32_t bb[UNROLL], yy[UNROLL], xx[UNROLL];
     bool live[UNROLL];
@@ -606,6 +608,10 @@ __global__ void __launch_bounds__(kThreads) k1_pixel(K1Args a, PlanarGeom g) {
         }
         bb[j] = b; yy[j] = y; xx[j] = x;
       }
+    }
+    if (need_lut) {
+      build_lut<T>(a, lut);
+      need_lut = false;
     }
 #pragma unroll
     for (int j = 0; j < UNROLL; ++j) {

@@ -112,6 +112,9 @@ def main():
                   for n in ((1, 2, 4) if sh == C2 else (1,))]
         cases += [dict(shape=C2, dtype=torch.float32, variant=v, streams=n) for v in ("bulk",) for n in (1, 2, 4)]
         cases += [dict(shape=C4, dtype=torch.float32, variant="bulk")]
+    elif len(sys.argv) > 1 and sys.argv[1] == "odd":
+        cases = [dict(shape=sh, dtype=dt, tune=t, streams=n) for sh in ((8, 481, 641, 4), (64, 481, 641, 4), (8, 481, 641, 3))
+                 for dt in (torch.float32, torch.bfloat16) for t in (0, 0x40000) for n in (1, 4)] * 2
     elif len(sys.argv) > 1 and sys.argv[1] == "nhwc_lf":
         cases = [dict(shape=sh, dtype=dt, layout="NHWC", tune=t, streams=n) for sh in (C2, (64, 480, 640, 4), C5, C4)
                  for dt in (torch.float32, torch.uint8, torch.bfloat16) for t in (0, 0x40000)
