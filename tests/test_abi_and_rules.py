@@ -104,3 +104,20 @@ def test_synthetic_generators_agree_with_oracle_copy():
         for k in a:
             np.testing.assert_array_equal(np.asarray(a[k]), np.asarray(b[k]))
     np.testing.assert_array_equal(S.gradient_frame(5, 7), O.gradient_frame(5, 7))
+
+
+def _build_c_demo(out):
+    from blendtorch.btt import native as N
+    cuda = Path("/usr/local/cuda")
+    cmd = ["gcc", "-O2", "-Wall", "-Werror", "-std=c99", "-I", str(ROOT / "include"), "-I", str(cuda / "include"),
+           str(ROOT / "examples" / "c_abi_demo.c"), "-L", str(N._LIB_PATH.parent), "-lbt_b200",
+           "-L", str(cuda / "lib64"), "-lcudart", "-lm", "-Wl,-rpath," + str(N._LIB_PATH.parent), "-o", str(out)]
+    subprocess.run(cmd, check=True, capture_output=True, text=True)
+    return out
+
+
+def test_header_is_plain_c_and_a_c_program_links(tmp_path):
+    """include/bt_b200.h must be usable without C++, torch or Python: examples/c_abi_demo.c is compiled as
+    C99 with -Werror and linked against the library (it is run on the GPU box by the gpu suite)."""
+    exe = _build_c_demo(tmp_path / "c_abi_demo")
+    assert exe.exists()

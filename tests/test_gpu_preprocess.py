@@ -247,3 +247,14 @@ def test_gather_index_matches_oracle_on_every_variant():
     assert none.shape[0] == 0
     with pytest.raises(ValueError):
         btt.preprocess_images(src, btt.Preprocess(), index=index.to(torch.int32))
+
+
+def test_c_program_drives_the_abi_without_python(tmp_path):
+    """examples/c_abi_demo.c: cudaMalloc + bt_preprocess_launch from plain C, checked in C against the
+    reference's expression (exit status 0 = every value bit-identical)."""
+    import subprocess
+    from test_abi_and_rules import _build_c_demo
+    exe = _build_c_demo(tmp_path / "c_abi_demo")
+    res = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stdout + res.stderr
+    assert "0 of" in res.stdout
