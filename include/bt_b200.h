@@ -329,6 +329,13 @@ int bt_preprocess_launch(const bt_preprocess_params* p, void* stream);
 int bt_preprocess_last_variant(void);
 int bt_preprocess_last_kernels(void);
 
+/* Vertical flip of frames of any element type: dst[b][y][:] = src[src_index ? src_index[b] : b][height-1-y][:],
+ * rows of row_bytes bytes, dense images.  For fields K1 does not take (a float32 depth map read back
+ * bottom-up has the same order as the colour buffer that pkg_blender/blendtorch/btb/offscreen.py:95-96
+ * flips with np.flipud; BASELINE config 3 carries such a map).  A copy at HBM speed. */
+int bt_flip_rows_launch(const void* src, void* dst, int batch, int height, uint64_t row_bytes, const int64_t* src_index,
+                        void* stream);
+
 /* K1 with per-batch statistics for callers that cannot allocate device memory.
  * (No counterpart in the reference: it never touches the device.)
  *

@@ -40,7 +40,7 @@ from . import shm
 from . import wire
 from .dataset import FileDataset, RemoteIterableDataset, open_pull_socket
 from .file import FileRecorder
-from .preprocess import PreparedPreprocess, Preprocess
+from .preprocess import FlipRows, Preprocess, prepare
 from .rx import DirectReceiver, Receiver, direct_capable
 from .staging import Ring, Schema, refuse_pickle
 
@@ -79,10 +79,7 @@ class _ResidentCache:
     def _allocate(self, schema, n, device, specs):
         for c in schema.columns:
             dt = _torch_dtype(c.dtype)
-            prep = None
-            if c.key in specs:
-                shp = c.shape if len(c.shape) == 3 else c.shape + (1,)
-                prep = PreparedPreprocess(specs[c.key], shp[0], shp[1], shp[2], device)
+            prep = prepare(specs[c.key], c.shape, c.dtype, dt, device) if c.key in specs else None
             self.plan.append((c.key, prep))
             self.cols[c.key] = torch.empty((n,) + tuple(c.shape), dtype=dt, device=device)
 
@@ -131,12 +128,7 @@ class _Stager:
         self.plan = []
         for c in schema.columns:
             spec = specs.get(c.key)
-            prep = None
-            if spec is not None:
-                shp = c.shape if len(c.shape) == 3 else c.shape + (1,)
-                if len(shp) != 3:
-                    raise ValueError("field %r has shape %s; frames are (H,W,C) or (H,W)" % (c.key, list(c.shape)))
-                prep = PreparedPreprocess(spec, shp[0], shp[1], shp[2], device)
+            prep = prepare(spec, c.shape, c.dtype, _torch_dtype(c.dtype), device) if spec is not None else None
             self.plan.append((c.key, c.slot_off, c.item_bytes, _torch_dtype(c.dtype), c.shape, prep))
         self.item_bytes = sum(c.item_bytes for c in schema.columns)
 
@@ -265,7 +257,8 @@ class DeviceLoader:
         `FileDataset`; streams cannot be shuffled, generate.py:71-72).
     device: CUDA device of this process (one process per GPU; shard publishers/files with `shard`).
     preprocess: a `Preprocess` or list of them (one per image field) run on the GPU; None leaves
-        the uint8 frames as they are -- exactly default_collate's output, on the device.
+        the uint8 frames as they are -- exactly default_collate's output, on the device.  A `FlipRows`
+        in the list flips a field of any dtype vertically (depth maps sent bottom-up).
     project: a `Projection` or list of them: world points carried by the messages are projected to
         pixels (and per-object boxes) on the GPU, one K2 launch per batch.
     num_receivers: receiver threads for streams (default 1); each owns a PULL socket connected to all
@@ -317,7 +310,7 @@ class DeviceLoader:
             self.device = torch.device("cuda", torch.cuda.current_device())
         if preprocess is None:
             preprocess = []
-        elif isinstance(preprocess, Preprocess):
+        elif isinstance(preprocess, (Preprocess, FlipRows)):
             preprocess = [preprocess]
         self.specs = {p.key: p for p in preprocess}
         if project is None:
@@ -375,10 +368,10 @@ class DeviceLoader:
         (page-locking hundreds of MB takes longer than an epoch of small recordings), so a stager
         is kept per producer and reused by later epochs while the layout stays the same."""
         schema = Schema.from_message(first_msg, self.batch_size, sizes, self.allow_pickle)
-        for key in self.specs:
+        for key, spec in self.specs.items():
             c = schema.column(key)  # KeyError: the named image field is not in the messages
-            if c.dtype != np.uint8:
-                raise TypeError("field %r is %s; preprocessing takes uint8 frames" % (key, c.dtype))
+            if c.dtype != np.uint8 and not isinstance(spec, FlipRows):
+                raise TypeError("field %r is %s; Preprocess takes uint8 frames (FlipRows flips anything)" % (key, c.dtype))
         depth = self.ring_depth if depth is None else depth
         sig = (schema.native, tuple((c.key, c.kind, c.dtype.str, c.shape, c.slot_off) for c in schema.columns),
                schema.host_keys, depth)

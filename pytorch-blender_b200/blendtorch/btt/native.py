@@ -131,6 +131,7 @@ def _load():
         "bt_preprocess_launch": (i32, [C.POINTER(PreprocessParams), vp]),
         "bt_preprocess_last_variant": (i32, []),
         "bt_preprocess_last_kernels": (i32, []),
+        "bt_flip_rows_launch": (i32, [vp, vp, i32, i32, u64, vp, vp]),
         "bt_preprocess_stats_static": (i32, [C.POINTER(PreprocessParams), vp]),
         "bt_project_launch": (i32, [C.POINTER(ProjectParams), vp]),
         "bt_device_count": (i32, [C.POINTER(i32)]),
@@ -157,7 +158,7 @@ EXPORTS = ["bt_last_error", "bt_abi_version", "bt_scan_message", "bt_schema_crea
            "bt_shm_create", "bt_shm_attach", "bt_shm_close", "bt_shm_nslots", "bt_shm_slot_bytes",
            "bt_shm_slot_ptr", "bt_shm_acquire", "bt_shm_release",
            "bt_build_gamma_lut", "bt_preprocess_scratch_bytes", "bt_preprocess_launch",
-           "bt_preprocess_last_variant", "bt_preprocess_last_kernels", "bt_preprocess_stats_static", "bt_project_launch", "bt_raster_launch", "bt_device_count", "bt_measure_h2d"]
+           "bt_preprocess_last_variant", "bt_preprocess_last_kernels", "bt_flip_rows_launch", "bt_preprocess_stats_static", "bt_project_launch", "bt_raster_launch", "bt_device_count", "bt_measure_h2d"]
 
 
 def last_error():

@@ -215,3 +215,69 @@ class PreparedPreprocess:
         if stats is not None:
             self.last_kernels = N.lib.bt_preprocess_last_kernels()
         return out, stats
+
+
+@dataclass
+class FlipRows:
+    """Vertical flip of a field K1 does not take -- a float32 depth map, a uint16 mask -- sent bottom-up.
+    The colour buffer of the reference is flipped on the producer (btb/offscreen.py:95-96); a depth
+    read-back has the same order.  One copy at HBM speed (``bt_flip_rows_launch``), any dtype and shape
+    (items are (H, ...) arrays, rows are everything after the first axis)."""
+    key: str = "depth"
+
+
+def flip_rows(src, out=None, stream=None, index=None):
+    """``torch.flip(src, dims=[1])`` for a contiguous CUDA tensor (B, H, ...) -- or, with `index`, of
+    ``src[index]`` -- by the library's kernel."""
+    if not src.is_cuda or not src.is_contiguous() or src.dim() < 2:
+        raise ValueError("flip_rows takes a contiguous CUDA tensor of shape (B, H, ...)")
+    n = src.shape[0] if index is None else index.numel()
+    if index is not None and (not index.is_cuda or index.dtype != torch.int64 or not index.is_contiguous()):
+        raise ValueError("index must be a contiguous CUDA int64 tensor")
+    shape = (n,) + tuple(src.shape[1:])
+    if out is None:
+        out = torch.empty(shape, dtype=src.dtype, device=src.device)
+    elif tuple(out.shape) != shape or out.dtype != src.dtype or not out.is_contiguous():
+        raise ValueError("out must be a contiguous %s tensor of shape %s" % (src.dtype, shape))
+    if out.numel():
+        h = src.shape[1]
+        row_bytes = src[0, 0].numel() * src.element_size() if src.dim() > 2 else src.element_size()
+        with torch.cuda.device(src.device):
+            N.check(N.lib.bt_flip_rows_launch(src.data_ptr(), out.data_ptr(), n, h, row_bytes,
+                                              index.data_ptr() if index is not None else None, _stream_handle(stream)))
+    return out
+
+
+class PreparedFlip:
+    """`flip_rows` for a fixed item shape; same calling convention as `PreparedPreprocess`."""
+
+    def __init__(self, spec, shape, dtype, device):
+        if len(shape) < 1:
+            raise ValueError("field %r is a scalar; there are no rows to flip" % spec.key)
+        self.spec, self.device, self.shape, self.dtype = spec, device, tuple(shape), dtype
+        self.h = shape[0]
+        self.row_bytes = int(torch.empty(0, dtype=dtype).element_size())
+        for d in shape[1:]:
+            self.row_bytes *= d
+        self.last_kernels = 0
+
+    def run(self, src_ptr, n, stream_handle, index_ptr=None):
+        out = torch.empty((n,) + self.shape, dtype=self.dtype, device=self.device)
+        self.last_kernels = 0
+        if out.numel():
+            N.check(N.lib.bt_flip_rows_launch(src_ptr, out.data_ptr(), n, self.h, self.row_bytes, index_ptr, stream_handle))
+            self.last_kernels = 1
+        return out, None
+
+
+def prepare(spec, shape, np_dtype, torch_dtype, device):
+    """The per-stream launcher of a field's spec (`Preprocess` or `FlipRows`) for items of `shape`."""
+    import numpy as np
+    if isinstance(spec, FlipRows):
+        return PreparedFlip(spec, shape, torch_dtype, device)
+    if np_dtype != np.uint8:
+        raise TypeError("field %r is %s; Preprocess takes uint8 frames (FlipRows flips anything)" % (spec.key, np_dtype))
+    shp = tuple(shape) if len(shape) == 3 else tuple(shape) + (1,)
+    if len(shp) != 3:
+        raise ValueError("field %r has shape %s; frames are (H,W,C) or (H,W)" % (spec.key, list(shape)))
+    return PreparedPreprocess(spec, shp[0], shp[1], shp[2], device)

@@ -634,6 +634,52 @@ __global__ void __launch_bounds__(kThreads) k1_pixel(K1Args a, PlanarGeom g) {
   if (STATS) finish_stats(a, acc);
 }
 
+// ---- row flip for frames of any element type (depth maps) ------------------------------------------
+// dst[b][y] = src[index ? index[b] : b][H-1-y], rows of `upr` units of UB bytes.  A copy: HBM-bound,
+// one 16-byte load and one 16-byte streaming store per unit when rows are whole 16-byte units.
+struct FlipArgs {
+  const uint8_t* src;
+  uint8_t* dst;
+  const long long* src_index;
+  uint64_t row_bytes, image_bytes;
+  uint32_t H;
+};
+
+template <int UB, int UNROLL>
+__global__ void __launch_bounds__(kThreads) k1_flip_rows(FlipArgs a, PlanarGeom g) {
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t u0 = blockIdx.x * blockDim.x + threadIdx.x; u0 < g.total_units; u0 += stride * UNROLL) {
+    uint32_t w[UNROLL][UB >= 4 ? UB / 4 : 1];
+    uint64_t out_off[UNROLL];
+    bool live[UNROLL];
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      const uint32_t u = u0 + j * stride;
+      live[j] = u < g.total_units && u >= u0;
+      if (live[j]) {
+        const uint32_t row = fdiv(u, g.upr);
+        const uint32_t ux = u - row * g.upr.div;
+        const uint32_t b = fdiv(row, g.rows);
+        const uint32_t y = row - b * g.rows.div;
+        const uint64_t img = a.src_index ? (uint64_t)__ldg(a.src_index + b) : (uint64_t)b;
+        const uint8_t* sp = a.src + img * a.image_bytes + (uint64_t)(a.H - 1 - y) * a.row_bytes + (uint64_t)ux * UB;
+        if constexpr (UB >= 4) ld_words<UB>(sp, w[j]);
+        else w[j][0] = __ldg(sp);
+        out_off[j] = (uint64_t)row * a.row_bytes + (uint64_t)ux * UB;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < UNROLL; ++j) {
+      if (!live[j]) continue;
+      if constexpr (UB == 16) __stcs(reinterpret_cast<uint4*>(a.dst + out_off[j]), make_uint4(w[j][0], w[j][1], w[j][2], w[j][3]));
+      else if constexpr (UB == 4) __stcs(reinterpret_cast<unsigned int*>(a.dst + out_off[j]), w[j][0]);
+      else a.dst[out_off[j]] = (uint8_t)w[j][0];
+    }
+  }
+}
+
 thread_local int g_last_variant = 0;
 thread_local int g_last_kernels = 0;
 
@@ -927,6 +973,36 @@ uint64_t bt_preprocess_scratch_bytes(const bt_preprocess_params* p) {
 
 int bt_preprocess_last_variant(void) { return g_last_variant; }
 int bt_preprocess_last_kernels(void) { return g_last_kernels; }
+
+int bt_flip_rows_launch(const void* src, void* dst, int batch, int height, uint64_t row_bytes, const int64_t* src_index,
+                        void* stream) {
+  if (!src || !dst) return bt::fail(BT_E_INVALID, "bt_flip_rows_launch: null pointer");
+  if (batch < 0 || height < 0) return bt::fail(BT_E_INVALID, "negative extent");
+  if ((uint64_t)batch * height * row_bytes == 0) return BT_OK;
+  FlipArgs a;
+  a.src = static_cast<const uint8_t*>(src);
+  a.dst = static_cast<uint8_t*>(dst);
+  a.src_index = reinterpret_cast<const long long*>(src_index);
+  a.row_bytes = row_bytes;
+  a.image_bytes = row_bytes * (uint64_t)height;
+  a.H = (uint32_t)height;
+  const bool al16 = row_bytes % 16 == 0 && reinterpret_cast<uintptr_t>(src) % 16 == 0 && reinterpret_cast<uintptr_t>(dst) % 16 == 0;
+  const bool al4 = row_bytes % 4 == 0 && reinterpret_cast<uintptr_t>(src) % 4 == 0 && reinterpret_cast<uintptr_t>(dst) % 4 == 0;
+  const uint32_t ub = al16 ? 16 : al4 ? 4 : 1;
+  const uint64_t upr = row_bytes / ub, total = (uint64_t)batch * height * upr;
+  if (total >= (1ull << 31)) return bt::fail(BT_E_TOO_LARGE, "bt_flip_rows_launch: more than 2^31 units in one launch; split the batch");
+  PlanarGeom geo;
+  geo.upr = make_fastdiv((uint32_t)upr);
+  geo.rows = make_fastdiv((uint32_t)height);
+  geo.total_units = (uint32_t)total;
+  const int g = grid_for((total + 3) / 4, sm_count(), kDefaultCtasPerSm);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (ub == 16) k1_flip_rows<16, 4><<<g, kThreads, 0, st>>>(a, geo);
+  else if (ub == 4) k1_flip_rows<4, 4><<<g, kThreads, 0, st>>>(a, geo);
+  else k1_flip_rows<1, 4><<<g, kThreads, 0, st>>>(a, geo);
+  BT_CUDA_TRY(cudaGetLastError());
+  return BT_OK;
+}
 
 int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) { return launch_checked(p, stream, kStatsMaxRows); }
 

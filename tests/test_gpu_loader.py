@@ -467,3 +467,29 @@ def test_allow_pickle_false_never_unpickles():
     with pytest.raises(ValueError, match="allow_pickle=False"):
         btt.DeviceLoader(btt.RemoteIterableDataset(["tcp://127.0.0.1:1"], item_transform=lambda x: x), device=DEV,
                          allow_pickle=False)
+
+
+def test_depth_field_is_flipped_with_fliprows(tmp_path):
+    """BASELINE config 3 carries a float32 depth map next to the frame: a FlipRows spec flips it on the GPU
+    like the frame (both are bottom-up after a GL read-back), in the pipeline and from resident caches."""
+    from oracle import btr
+    prefix = str(tmp_path / "c3")
+    S.write_recordings(prefix, config=3, n_files=1, frames_per_file=6, h=24, w=32)
+    ref = btr.ReplayDataset(prefix)
+    ds = btt.FileDataset(prefix)
+    specs = [btt.Preprocess(flip=True, mean=127.5, std=127.5), btt.FlipRows("depth")]
+    for cache in (None, "device", "host"):
+        dl = btt.DeviceLoader(ds, batch_size=4, device=DEV, preprocess=specs, cache=cache, keep_raw=True)
+        for epoch in range(2):
+            n = 0
+            for b in dl:
+                for i in range(len(b["depth"])):
+                    np.testing.assert_array_equal(b["depth"][i].cpu().numpy(), ref[n + i]["depth"][::-1])
+                    np.testing.assert_array_equal(b["depth_raw"][i].cpu().numpy(), ref[n + i]["depth"])
+                    np.testing.assert_array_equal(b["image"][i].cpu().numpy(),
+                                                  opre.preprocess_frame(ref[n + i]["image"], flip=True, mean=127.5, std=127.5))
+                n += len(b["depth"])
+            assert n == 6
+        dl.close()
+    with pytest.raises(TypeError, match="uint8"):
+        list(btt.DeviceLoader(ds, batch_size=4, device=DEV, preprocess=btt.Preprocess(key="depth")))

@@ -258,3 +258,21 @@ def test_c_program_drives_the_abi_without_python(tmp_path):
     res = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
     assert res.returncode == 0, res.stdout + res.stderr
     assert "0 of" in res.stdout
+
+
+def test_flip_rows_any_dtype_and_gather():
+    """bt_flip_rows_launch == torch.flip(dims=[1]) for float32 depth maps, odd row sizes (4- and 1-byte
+    units), uint16 masks, and with a gather index."""
+    g = torch.Generator(device=DEV)
+    g.manual_seed(3)
+    cases = [((5, 9, 16), torch.float32), ((3, 7, 5), torch.float32), ((2, 6, 7), torch.uint8), ((4, 5, 3, 2), torch.int16),
+             ((2, 1080, 1920), torch.float32), ((3, 1, 8), torch.float64), ((0, 4, 4), torch.float32)]
+    for shape, dt in cases:
+        src = (torch.rand(shape, device=DEV, generator=g) * 1000).to(dt)
+        out = btt.flip_rows(src)
+        assert torch.equal(out, torch.flip(src, dims=[1])), (shape, dt)
+        if shape[0] > 1:
+            idx = torch.tensor([shape[0] - 1, 0, 0], device=DEV)
+            assert torch.equal(btt.flip_rows(src, index=idx), torch.flip(src[idx], dims=[1]))
+    with pytest.raises(ValueError):
+        btt.flip_rows(torch.zeros(4, device=DEV))
