@@ -71,6 +71,27 @@ def spawn_publishers(module, n, transport="tcp", tag="p", extra=()):
     return addrs, procs
 
 
+def spawn_native_publisher(n, transport="tcp", threads=1, tag="n", extra=(), cpus=None, config=None, h=None, w=None):
+    """One process hosting `n` publishers on the library's own PUSH endpoints (bt_push_*), `threads`
+    sender threads.  Returns (addresses, process)."""
+    env = dict(os.environ)
+    env["PYTHONPATH"] = os.pathsep.join([str(ROOT), str(PKG), env.get("PYTHONPATH", "")])
+    addrs = []
+    for i in range(n):
+        if transport == "ipc":
+            addrs.append("ipc:///tmp/bt_bench_%d_%s_%d" % (os.getpid(), tag, i))
+        else:
+            addrs.append("tcp://127.0.0.1:%d" % free_port())
+    cmd = [sys.executable, "-m", "blendtorch.btt.synthetic", "--native", "--threads", str(threads), "--btid", "0",
+           "--config", str(CONFIG if config is None else config), "--height", str(h or H), "--width", str(w or W), *extra]
+    for a in addrs:
+        cmd += ["--bind", a]
+    if cpus:
+        cmd += ["--cpus", ",".join(str(c) for c in cpus)]
+    proc = subprocess.Popen(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return addrs, proc
+
+
 def stop_publishers(procs):
     for p in procs:
         try:

@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define BT_ABI_VERSION 2
+#define BT_ABI_VERSION 3
 
 typedef enum bt_status {
   BT_OK = 0,
@@ -254,21 +254,91 @@ int bt_pull_fill(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, i
  * No counterpart in the reference, whose only transport is the pickled ZMQ message
  * (btb/publisher.py:43).  A producer writes each large array into a slot of a POSIX shared-memory
  * segment and sends, over the same ZMQ socket, the usual pickled dict with the array replaced by the
- * tuple ("__btshm__", segment_name, slot, dtype_str, shape).  The consumer maps the segment once,
+ * tuple ("__btshm__", segment_name, ticket, dtype_str, shape).  The consumer maps the segment once,
  * page-locks it with cudaHostRegister, and copies slots to the device by DMA: zero CPU copies on the
  * consumer side.  A slot is busy from bt_shm_acquire (producer) until bt_shm_release (consumer).
+ *
+ * ticket = slot | generation << 16.  Every hand-out of a slot bumps its generation with a
+ * compare-and-swap (several producers may share a segment), the ticket travels in the message, and
+ * the consumer compares generations before and after it reads the slot (bt_shm_check; bt_shm_release
+ * is a compare-and-swap on the same word).  So a slot that its producer took back while a slow
+ * consumer still held a reference is *detected* (BT_E_IO from the ingest / ring calls), not read as if
+ * nothing had happened, and the late release cannot free the slot under its new owner.
+ * Taking slots back: bt_shm_acquire reuses a busy slot once it has been held longer than the
+ * segment's lease (default 30 s, environment BT_SHM_LEASE_MS at creation, bt_shm_set_lease; 0 =
+ * never).  That protects producers from consumers that died with messages queued; it is lossy for
+ * a live consumer that is slower than the lease, which then fails loudly as described.
+ * Functions that take `ticket` also accept a bare slot number (generation 0 = compare nothing).
  * ------------------------------------------------------------------------------------------ */
 typedef struct bt_shm bt_shm;
 
-int bt_shm_create(const char* name, uint64_t slot_bytes, int nslots, bt_shm** out); /* producer */
+int bt_shm_create(const char* name, uint64_t slot_bytes, int nslots, bt_shm** out); /* producer; nslots <= 65536 */
 int bt_shm_attach(const char* name, int device, bt_shm** out); /* consumer; device >= 0 page-locks it */
 int bt_shm_close(bt_shm* s);                                    /* creator also unlinks the name */
 int bt_shm_nslots(const bt_shm* s);
 uint64_t bt_shm_slot_bytes(const bt_shm* s);
-void* bt_shm_slot_ptr(bt_shm* s, int slot);
-/* Producer: next slot in round-robin order once it is free; BT_E_TIMEOUT after timeout_ms (<0: forever). */
-int bt_shm_acquire(bt_shm* s, int timeout_ms, int* slot);
-int bt_shm_release(bt_shm* s, int slot);
+void* bt_shm_slot_ptr(bt_shm* s, int ticket);
+/* Producer: ticket of the first free slot in round-robin order; BT_E_TIMEOUT after timeout_ms
+ * (<0: wait forever, 0: poll once). */
+int bt_shm_acquire(bt_shm* s, int timeout_ms, int* ticket);
+int bt_shm_set_lease(bt_shm* s, int64_t lease_ms);
+/* Consumer: BT_OK while the slot still belongs to this ticket, BT_E_IO once it was taken back. */
+int bt_shm_check(const bt_shm* s, int ticket);
+/* Consumer: free the slot; BT_E_IO (and no effect) when the ticket is stale. */
+int bt_shm_release(bt_shm* s, int ticket);
+
+/* ------------------------------------------------------------------------------------------
+ * Native publisher: a minimal ZMTP 3 PUSH endpoint (tcp:// and ipc://, NULL security), the producer
+ * end of the ingest wire without libzmq or an interpreter per producer.
+ * Replaces pkg_blender/blendtorch/btb/publisher.py:21-43 (`DataPublisher`: PUSH socket, bind,
+ * SNDHWM, IMMEDIATE=1, `send_pyobj`) for producers that already hold pickled messages (replaying
+ * recordings, synthetic load, simulators written in C): messages go from the caller's memory to
+ * the kernel socket with one copy, framed exactly as libzmq frames them, so unmodified
+ * `btt.RemoteIterableDataset` consumers (pkg_pytorch/blendtorch/btt/dataset.py:73-78,98-105) and the
+ * direct receiver above take them alike.  Semantics kept from the reference's socket options:
+ * messages only go to peers whose connection is complete (IMMEDIATE=1, publisher.py:26), peers are
+ * served round-robin skipping those that cannot take more (PUSH load balancing), and the sender
+ * blocks when no peer can take a message (SNDHWM back-pressure, publisher.py:24; the queue here is
+ * the kernel socket buffer plus one message in progress per peer).
+ * One bt_push holds any number of bound endpoints ("publishers"); an endpoint must be driven by one
+ * thread at a time.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct bt_push bt_push;
+
+int bt_push_create(bt_push** out);
+/* Bind one more endpoint ("tcp://host:port", port 0 or "*" = any free port; "ipc://path").  Returns
+ * its index (>= 0).  bt_push_endpoint gives the address peers connect to (resolved port). */
+int bt_push_bind(bt_push* p, const char* address);
+int bt_push_endpoint(bt_push* p, int endpoint, char* address_out, int capacity);
+int bt_push_destroy(bt_push* p);
+/* Peers of `endpoint` whose handshake is complete (accepts pending connections first). */
+int bt_push_peers(bt_push* p, int endpoint);
+/* Send one message of `nparts` frames (1 = the reference wire; more = the raw-parts wire, frame 0 the
+ * pickled header) to the next peer that can take it; blocks up to timeout_ms (<0: forever) while no
+ * peer is connected or every peer's socket is full, then BT_E_TIMEOUT. */
+int bt_push_send(bt_push* p, int endpoint, const uint8_t* const* parts, const uint64_t* lens, int nparts, int timeout_ms);
+/* Synthetic load / replay loop, to be called from one thread per disjoint endpoint range: endpoint e in
+ * [first, first + count) sends messages pool[e - first][0..pool_n) in a cycle, `messages` of them (<0:
+ * until *stop becomes non-zero), keeping every connected peer's socket busy.  pool is an array of
+ * count * pool_n (pointer, length) pairs, endpoint-major.
+ * With `seg` non-null the payload goes over the shared-memory wire instead: for message m,
+ * payload[m] (payload_len[m] bytes) is copied into a free slot and tmpl[m] -- the pickled message with
+ * the array replaced by ("__btshm__", name, ticket, dtype, shape), whose ticket is a 4-byte BININT at
+ * byte tmpl_ticket_off[m] -- is sent with that slot's ticket patched in.
+ * *sent (optional) is updated as messages go out.  Returns BT_OK when all were sent or stop was seen. */
+typedef struct bt_push_job {
+  int first_endpoint, n_endpoints, pool_n, reserved;
+  int64_t messages;                 /* per endpoint; < 0: until stopped */
+  const uint8_t* const* pool;       /* [n_endpoints * pool_n] messages (or templates when seg != NULL) */
+  const uint64_t* pool_len;
+  bt_shm* const* seg;               /* NULL, or one segment per endpoint */
+  const uint8_t* const* payload;    /* [n_endpoints * pool_n] array bytes for the shared-memory wire */
+  const uint64_t* payload_len;
+  const uint32_t* tmpl_ticket_off;  /* [n_endpoints * pool_n] */
+  volatile int* stop;               /* may be NULL */
+  volatile int64_t* sent;           /* may be NULL; total over the range */
+} bt_push_job;
+int bt_push_run(bt_push* p, const bt_push_job* job);
 
 /* ------------------------------------------------------------------------------------------
  * K1: fused frame preprocessing on the device.

@@ -5,7 +5,8 @@ uint8 RGBA frames, `xy` float64, bboxes float32 from sorted pairs, depth float32
 in [0.1, 100), cube centres in the range of
 examples/datagen/falling_cubes.blend.py:21.  The product package carries its own
 generator (blendtorch/btt/synthetic.py) because it may not import the oracle;
-tests/test_synthetic.py checks that the two emit identical bytes.
+tests/test_abi_and_rules.py::test_synthetic_generators_agree_with_oracle_copy checks that the two emit
+identical values.
 """
 
 import pickle

@@ -72,6 +72,13 @@ class ProjectParams(C.Structure):
                 ("bbox_out", C.c_void_p)]
 
 
+class PushJob(C.Structure):
+    _fields_ = [("first_endpoint", C.c_int32), ("n_endpoints", C.c_int32), ("pool_n", C.c_int32), ("reserved", C.c_int32),
+                ("messages", C.c_int64), ("pool", C.c_void_p), ("pool_len", C.c_void_p),
+                ("seg", C.c_void_p), ("payload", C.c_void_p), ("payload_len", C.c_void_p),
+                ("tmpl_ticket_off", C.c_void_p), ("stop", C.c_void_p), ("sent", C.c_void_p)]
+
+
 def _load():
     if not _LIB_PATH.exists():
         raise ImportError(
@@ -118,6 +125,13 @@ def _load():
         "bt_pull_pending_parts": (i32, [vp, C.POINTER(u64), i32]),
         "bt_pull_drop": (i32, [vp]),
         "bt_pull_fill": (i32, [vp, vp, i32, vp, i32, i32, i32, C.POINTER(i32)]),
+        "bt_push_create": (i32, [C.POINTER(vp)]),
+        "bt_push_bind": (i32, [vp, C.c_char_p]),
+        "bt_push_endpoint": (i32, [vp, i32, C.c_char_p, i32]),
+        "bt_push_destroy": (i32, [vp]),
+        "bt_push_peers": (i32, [vp, i32]),
+        "bt_push_send": (i32, [vp, i32, vp, vp, i32, i32]),
+        "bt_push_run": (i32, [vp, C.POINTER(PushJob)]),
         "bt_shm_create": (i32, [C.c_char_p, u64, i32, C.POINTER(vp)]),
         "bt_shm_attach": (i32, [C.c_char_p, i32, C.POINTER(vp)]),
         "bt_shm_close": (i32, [vp]),
@@ -126,6 +140,8 @@ def _load():
         "bt_shm_slot_ptr": (vp, [vp, i32]),
         "bt_shm_acquire": (i32, [vp, i32, C.POINTER(i32)]),
         "bt_shm_release": (i32, [vp, i32]),
+        "bt_shm_check": (i32, [vp, i32]),
+        "bt_shm_set_lease": (i32, [vp, C.c_int64]),
         "bt_build_gamma_lut": (i32, [C.c_double, C.POINTER(C.c_uint8 * 256)]),
         "bt_preprocess_scratch_bytes": (u64, [C.POINTER(PreprocessParams)]),
         "bt_preprocess_launch": (i32, [C.POINTER(PreprocessParams), vp]),
@@ -155,8 +171,10 @@ EXPORTS = ["bt_last_error", "bt_abi_version", "bt_scan_message", "bt_schema_crea
            "bt_rx_release_queued",
            "bt_pull_create", "bt_pull_connect", "bt_pull_destroy", "bt_pull_recv", "bt_pull_pending", "bt_pull_pending_parts",
            "bt_pull_drop", "bt_pull_fill",
+           "bt_push_create", "bt_push_bind", "bt_push_endpoint", "bt_push_destroy", "bt_push_peers", "bt_push_send",
+           "bt_push_run",
            "bt_shm_create", "bt_shm_attach", "bt_shm_close", "bt_shm_nslots", "bt_shm_slot_bytes",
-           "bt_shm_slot_ptr", "bt_shm_acquire", "bt_shm_release",
+           "bt_shm_slot_ptr", "bt_shm_acquire", "bt_shm_release", "bt_shm_check", "bt_shm_set_lease",
            "bt_build_gamma_lut", "bt_preprocess_scratch_bytes", "bt_preprocess_launch",
            "bt_preprocess_last_variant", "bt_preprocess_last_kernels", "bt_flip_rows_launch", "bt_preprocess_stats_static", "bt_project_launch", "bt_raster_launch", "bt_device_count", "bt_measure_h2d"]
 

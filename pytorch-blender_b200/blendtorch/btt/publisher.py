@@ -89,3 +89,161 @@ class DataPublisher:
 
     def __exit__(self, *a):
         self.close()
+
+
+class NativePublisher:
+    """Several publishers in one process without libzmq: the library's own ZMTP PUSH endpoints
+    (``bt_push_*``, csrc/push.cpp), for producers that already hold pickled messages -- replaying
+    recordings, synthetic load, simulators that are not Python.
+
+    Each bound address is one publisher in the sense of btb/publisher.py:21-27 (PUSH, bind, messages only
+    to completed connections, blocking when no consumer can take more); unmodified
+    ``btt.RemoteIterableDataset`` consumers and the direct receiver connect to them alike.  A message
+    goes from the caller's buffer to the kernel socket in one copy and the GIL is released while it
+    does, so a few threads of one process do the work of a process (plus libzmq I/O thread) per
+    publisher.
+
+        pub = NativePublisher(["tcp://127.0.0.1:*"] * 5)
+        pub.addresses                       # what consumers connect to
+        pub.publish_raw(blob, endpoint=2)   # one pickled message
+        pub.start(pools, threads=2)         # cycle pre-pickled pools on background threads
+    """
+
+    def __init__(self, bind_addresses):
+        import ctypes as C
+        from . import native as N
+        self._C, self._N = C, N
+        if isinstance(bind_addresses, str):
+            bind_addresses = [bind_addresses]
+        self.handle = C.c_void_p()
+        N.check(N.lib.bt_push_create(C.byref(self.handle)))
+        self.addresses = []
+        try:
+            for a in bind_addresses:
+                ep = N.check(N.lib.bt_push_bind(self.handle, a.encode()))
+                buf = C.create_string_buffer(256)
+                N.check(N.lib.bt_push_endpoint(self.handle, ep, buf, 256))
+                self.addresses.append(buf.value.decode())
+        except Exception:
+            self.close()
+            raise
+        self._threads, self._keep = [], []
+        self._stop = C.c_int(0)
+        self._sent = []
+
+    def peers(self, endpoint=0):
+        """Consumers connected to `endpoint` right now."""
+        return self._N.check(self._N.lib.bt_push_peers(self.handle, endpoint))
+
+    def publish_raw(self, data, endpoint=0, timeoutms=-1):
+        """Send one already pickled message (bytes-like); blocks while no consumer can take it."""
+        self.publish_parts([data], endpoint, timeoutms)
+
+    def publish_parts(self, frames, endpoint=0, timeoutms=-1):
+        """Send one message of several frames (the raw-parts wire, wire.py: header, then arrays)."""
+        C, N = self._C, self._N
+        n = len(frames)
+        ptrs, lens = (C.c_void_p * n)(), (C.c_uint64 * n)()
+        for i, f in enumerate(frames):
+            ptrs[i], lens[i] = N.buffer_address(f)
+        rc = N.lib.bt_push_send(self.handle, endpoint, ptrs, lens, n, int(timeoutms))
+        if rc == N.BT_E_TIMEOUT:
+            raise TimeoutError("no consumer took the message within %d ms" % timeoutms)
+        N.check(rc)
+
+    def start(self, pools, messages=-1, threads=1, shm=None):
+        """Cycle through pre-pickled `pools` (one list of bytes-like messages per endpoint, equal
+        lengths) on `threads` background threads, `messages` per endpoint (-1: until `stop`).
+
+        shm: None for the reference wire, or ``(segments, payloads, ticket_offsets)`` for the
+        shared-memory wire (shm.py): per endpoint a `shm.Segment`, per message the array that travels
+        through it and the byte offset of the 4-byte ticket inside the pickled template."""
+        import threading
+        C, N = self._C, self._N
+        n_ep = len(self.addresses)
+        if len(pools) != n_ep or len({len(p) for p in pools}) != 1:
+            raise ValueError("one pool per endpoint, all of the same length")
+        pool_n = len(pools[0])
+        threads = max(1, min(int(threads), n_ep))
+        bounds = [n_ep * t // threads for t in range(threads + 1)]
+        self._stop.value = 0
+        for t in range(threads):
+            first, count = bounds[t], bounds[t + 1] - bounds[t]
+            n = count * pool_n
+            ptrs, lens = (C.c_void_p * n)(), (C.c_uint64 * n)()
+            flat = [m for pool in pools[first:first + count] for m in pool]
+            for i, m in enumerate(flat):
+                ptrs[i], lens[i] = N.buffer_address(m)
+            job = N.PushJob()
+            job.first_endpoint, job.n_endpoints, job.pool_n, job.messages = first, count, pool_n, int(messages)
+            job.pool, job.pool_len = C.cast(ptrs, C.c_void_p), C.cast(lens, C.c_void_p)
+            keep = [ptrs, lens, flat]
+            if shm is not None:
+                segs, payloads, offs = shm
+                sh = (C.c_void_p * count)(*[s.handle for s in segs[first:first + count]])
+                pp, pl, po = (C.c_void_p * n)(), (C.c_uint64 * n)(), (C.c_uint32 * n)()
+                fp = [a for row in payloads[first:first + count] for a in row]
+                fo = [o for row in offs[first:first + count] for o in row]
+                for i, (a, o) in enumerate(zip(fp, fo)):
+                    pp[i], pl[i] = N.buffer_address(a)
+                    po[i] = o
+                job.seg, job.payload = C.cast(sh, C.c_void_p), C.cast(pp, C.c_void_p)
+                job.payload_len, job.tmpl_ticket_off = C.cast(pl, C.c_void_p), C.cast(po, C.c_void_p)
+                keep += [sh, pp, pl, po, fp, segs]
+            sent = C.c_int64(0)
+            job.stop = C.cast(C.pointer(self._stop), C.c_void_p)
+            job.sent = C.cast(C.pointer(sent), C.c_void_p)
+            self._sent.append(sent)
+            self._keep.append((job, keep))
+            th = threading.Thread(target=self._run, args=(job,), daemon=True, name="bt-push-%d" % t)
+            th.start()
+            self._threads.append(th)
+
+    def _run(self, job):
+        rc = self._N.lib.bt_push_run(self.handle, self._C.byref(job))
+        if rc != self._N.BT_OK:
+            self.error = self._N.last_error()
+
+    error = None
+
+    @property
+    def sent(self):
+        """Messages sent so far by `start`'s threads."""
+        return sum(s.value for s in self._sent)
+
+    def join(self, timeout=None):
+        """Wait for `start`'s threads (they end by themselves when `messages` is finite)."""
+        for th in self._threads:
+            th.join(timeout)
+        return not any(th.is_alive() for th in self._threads)
+
+    def stop(self):
+        self._stop.value = 1
+        for th in self._threads:
+            th.join()
+        self._threads = []
+        if self.error:
+            raise RuntimeError("native publisher: " + self.error)
+
+    def close(self):
+        if getattr(self, "_threads", None):
+            self._stop.value = 1
+            for th in self._threads:
+                th.join()
+            self._threads = []
+        if self.handle:
+            self._N.lib.bt_push_destroy(self.handle)
+            self.handle = None
+        self._keep = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -4,7 +4,11 @@ pickled ZMQ message, btb/publisher.py:43); see include/bt_b200.h `bt_shm_*`.
 
 A message on this wire is the usual pickled dict in which a large array is replaced by
 
-    ("__btshm__", segment_name, slot, dtype_str, shape)
+    ("__btshm__", segment_name, ticket, dtype_str, shape)
+
+where ``ticket = slot | generation << 16``: every hand-out of a slot has its own generation, so a
+consumer that holds a reference past the producer's lease (see `Segment.set_lease`) notices that the
+slot has moved on -- before and after it copies -- and raises instead of delivering another frame.
 
 Both ends must opt in: the producer with ``DataPublisher(..., shm_slots=N)``, the consumer by being
 this package (``DeviceLoader`` DMAs the slot straight to the GPU; host iteration copies it out).
@@ -39,21 +43,29 @@ class Segment:
             self._views.append(np.frombuffer((C.c_uint8 * self.slot_bytes).from_address(p), dtype=np.uint8))
 
     def acquire(self, timeout_ms=10000):
+        """Ticket (slot | generation << 16) of a free slot; waits up to `timeout_ms` for one."""
         s = C.c_int()
         N.check(N.lib.bt_shm_acquire(self.handle, int(timeout_ms), C.byref(s)))
         return s.value
 
-    def view(self, slot):
-        return self._views[slot]
+    def view(self, ticket):
+        return self._views[ticket & 0xFFFF]
+
+    def set_lease(self, lease_ms):
+        """How long a consumer may hold a slot before `acquire` takes it back (default 30 s, or
+        ``BT_SHM_LEASE_MS``; 0 = never).  Taking slots back keeps consumers that died with messages queued
+        from starving the producer, and is lossy: a live consumer slower than the lease loses those
+        frames -- loudly (its copy fails the generation check), never silently."""
+        N.check(N.lib.bt_shm_set_lease(self.handle, int(lease_ms)))
 
     def put(self, array, timeout_ms=10000):
         """Copy `array` into the next free slot and return the marker that announces it."""
         a = np.ascontiguousarray(array)
         if a.nbytes > self.slot_bytes:
             raise ValueError("array of %d bytes does not fit a %d-byte slot" % (a.nbytes, self.slot_bytes))
-        slot = self.acquire(timeout_ms)
-        self._views[slot][:a.nbytes] = a.reshape(-1).view(np.uint8)
-        return (MARKER, self.name, slot, a.dtype.str, tuple(a.shape))
+        ticket = self.acquire(timeout_ms)
+        self.view(ticket)[:a.nbytes] = a.reshape(-1).view(np.uint8)
+        return (MARKER, self.name, ticket, a.dtype.str, tuple(a.shape))
 
     def drain(self, timeout_ms):
         """Wait (up to `timeout_ms` per slot) until consumers have released every slot."""
@@ -92,8 +104,9 @@ def fetch(marker):
     p = N.lib.bt_shm_slot_ptr(h, int(slot))
     if not p or n > N.lib.bt_shm_slot_bytes(h):
         raise N.NativeError(N.BT_E_INVALID, "shared-memory reference out of range")
+    N.check(N.lib.bt_shm_check(h, int(slot)))      # still ours before the copy ...
     out = np.frombuffer((C.c_uint8 * n).from_address(p), dtype=np.uint8).copy().view(dt).reshape(shape)
-    N.check(N.lib.bt_shm_release(h, int(slot)))
+    N.check(N.lib.bt_shm_release(h, int(slot)))    # ... and after it (the release compares generations)
     return out
 
 

@@ -139,9 +139,78 @@ def run_publisher(bind, btid, config, h, w, c=4, count=-1, pool=16, protocol=3, 
     return i
 
 
+_TICKET_SENTINEL = 0x5A5A5A5A
+
+
+def shm_templates(objs, segment, protocol=3):
+    """For the native publisher's shared-memory mode: per message the pickled dict in which the largest
+    array is replaced by its shm.py marker, the array itself, and the byte offset of the marker's
+    ticket (a 4-byte BININT the publisher patches per send)."""
+    from . import shm
+    tmpls, payloads, offs = [], [], []
+    needle = b"J" + _TICKET_SENTINEL.to_bytes(4, "little")
+    for o in objs:
+        o = dict(o)
+        key = max((k for k, v in o.items() if isinstance(v, np.ndarray)), key=lambda k: o[k].nbytes)
+        a = np.ascontiguousarray(o[key])
+        o[key] = (shm.MARKER, segment.name, _TICKET_SENTINEL, a.dtype.str, tuple(a.shape))
+        blob = pickle.dumps(o, protocol=protocol)
+        at = blob.find(needle)
+        assert at >= 0 and blob.find(needle, at + 1) < 0
+        tmpls.append(blob)
+        payloads.append(a)
+        offs.append(at + 1)
+    return tmpls, payloads, offs
+
+
+def run_native_publishers(binds, btids, config, h, w, c=4, count=-1, pool=16, protocol=3, threads=1,
+                          shm_slots=0, ready=None, stop=None):
+    """All publishers of one consumer in this process: one `NativePublisher` endpoint per bind address,
+    cycling the same deterministic pools as `run_publisher`, on `threads` sender threads.  Blocks until
+    every endpoint has sent `count` messages, or (count < 0) until `stop` (a threading.Event) is set."""
+    from .publisher import NativePublisher
+    pub = NativePublisher(list(binds))
+    segs = []
+    try:
+        if shm_slots > 0:
+            from . import shm
+            pools, payloads, offs = [], [], []
+            for btid in btids:
+                rng = rng_for(config, btid)
+                objs = [message(rng, config, btid, i, h, w, c) for i in range(pool)]
+                big = max(v.nbytes for v in objs[0].values() if isinstance(v, np.ndarray))
+                seg = shm.Segment(big, shm_slots)
+                segs.append(seg)
+                t, p, o = shm_templates(objs, seg, protocol=protocol)
+                pools.append(t)
+                payloads.append(p)
+                offs.append(o)
+            pub.start(pools, messages=count, threads=threads, shm=(segs, payloads, offs))
+        else:
+            pools = [pickled_pool(config, btid, h, w, c, pool, protocol) for btid in btids]
+            pub.start(pools, messages=count, threads=threads)
+        if ready is not None:
+            ready(pub.addresses)
+        while not pub.join(0.2):
+            if stop is not None and stop.is_set():
+                break
+        sent = pub.sent
+        pub.stop()
+        return sent
+    finally:
+        pub.close()
+        for seg in segs:
+            seg.drain(2000)
+            seg.close()
+
+
 def main(argv=None):
     ap = argparse.ArgumentParser(description="synthetic blendtorch publisher")
-    ap.add_argument("--bind", required=True)
+    ap.add_argument("--bind", required=True, action="append",
+                    help="address to bind; several (with --native) = several publishers in this process")
+    ap.add_argument("--native", action="store_true", help="the library's own PUSH endpoints instead of pyzmq")
+    ap.add_argument("--threads", type=int, default=1, help="sender threads (--native)")
+    ap.add_argument("--cpus", default="", help="comma-separated cpu ids to run on (sched_setaffinity)")
     ap.add_argument("--btid", type=int, default=0)
     ap.add_argument("--config", type=int, default=2)
     ap.add_argument("--height", type=int, default=None)
@@ -158,6 +227,16 @@ def main(argv=None):
     h, w, c = a.height or h, a.width or w, a.channels or c
     import signal
     signal.signal(signal.SIGTERM, lambda *_: sys.exit(0))  # run `finally` blocks (unlink shared memory)
+    if a.cpus:
+        import os
+        os.sched_setaffinity(0, {int(x) for x in a.cpus.split(",")})
+    if a.native:
+        btids = list(range(a.btid, a.btid + len(a.bind)))
+        run_native_publishers(a.bind, btids, a.config, h, w, c, a.count, a.pool, a.protocol, a.threads, a.shm_slots)
+        return 0
+    if len(a.bind) != 1:
+        ap.error("several --bind addresses need --native")
+    a.bind = a.bind[0]
     run_publisher(a.bind, a.btid, a.config, h, w, c, a.count, a.pool, a.protocol, a.send_hwm, shm_slots=a.shm_slots,
                   raw_parts=a.raw_parts)
 

@@ -18,7 +18,7 @@ ROOT = HERE.parent
 CSRC = HERE / "csrc"
 OUT_DIR = HERE / "blendtorch" / "btt" / "_native"
 LIB = OUT_DIR / "libbt_b200.so"
-SOURCES = ["scan.cpp", "rx.cpp", "zmtp.cpp", "ring.cu", "shm.cu", "preprocess.cu", "project.cu", "raster.cu"]
+SOURCES = ["scan.cpp", "rx.cpp", "zmtp.cpp", "push.cpp", "ring.cu", "shm.cu", "preprocess.cu", "project.cu", "raster.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 

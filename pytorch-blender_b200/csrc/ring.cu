@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <string>
 #include <vector>
 
 #include "common.h"
@@ -29,9 +30,22 @@ struct bt_ring {
 };
 
 namespace {
-void release_refs(std::vector<bt::PendingRef>& v) {
-  for (const bt::PendingRef& r : v) bt_shm_release(r.seg, r.shm_slot);
+// Hand the shared-memory slots of `v` back to their producers.  The release is a compare-and-swap on
+// the slot's generation (shm.cu): if the producer took a slot back while we were still reading it
+// (held past its lease), the bytes we copied may belong to a newer frame -- that is reported
+// (BT_E_IO, message kept in bt_last_error), never passed over.
+int release_refs(std::vector<bt::PendingRef>& v) {
+  int rc = BT_OK;
+  std::string first;
+  for (const bt::PendingRef& r : v) {
+    if (bt_shm_release(r.seg, r.shm_slot) != BT_OK && rc == BT_OK) {
+      rc = BT_E_IO;
+      first = bt::last_error_ref();
+    }
+  }
   v.clear();
+  if (rc != BT_OK) bt::last_error_ref() = first;
+  return rc;
 }
 }  // namespace
 
@@ -128,8 +142,7 @@ int bt_ring_wait(bt_ring* r, int slot) {
     BT_CUDA_TRY(cudaEventSynchronize(r->done[slot]));
     r->in_flight[slot] = 0;
   }
-  release_refs(r->copying[slot]);
-  return BT_OK;
+  return release_refs(r->copying[slot]);
 }
 
 int bt_ring_acquire(bt_ring* r, int* slot) {
@@ -177,12 +190,12 @@ int bt_ring_spill(bt_ring* r, int slot, const bt_schema* s) {
     const bt_column& c = s->cols[p.column];
     memcpy(base + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot), p.nbytes);
   }
-  release_refs(r->pending[slot]);
-  return BT_OK;
+  return release_refs(r->pending[slot]);   // the release doubles as the "still ours after the copy" check
 }
 
 int bt_ring_submit_batch(bt_ring* r, int slot, const bt_schema* s, int n_items, void* dev_dst, void* stream) {
-  if (!r || !s || slot < 0 || slot >= r->depth || !dev_dst || n_items < 0 || n_items > s->batch)
+  if (!r || !s || slot < 0 || slot >= r->depth || !dev_dst || n_items < 0 || n_items > s->batch ||
+      s->slot_bytes > r->slot_bytes)
     return bt::fail(BT_E_INVALID, "bt_ring_submit_batch: bad arguments");
   if (!r->pinned) return bt::fail(BT_E_CUDA, "ring was created without a CUDA device; nothing to copy to");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -192,30 +205,47 @@ int bt_ring_submit_batch(bt_ring* r, int slot, const bt_schema* s, int n_items, 
   // how many items of each column arrived by reference
   std::vector<int> by_ref(s->cols.size(), 0);
   for (const bt::PendingRef& p : pend) by_ref[p.column]++;
+  // A failure part-way must not leave the slot looking free while copies already enqueued still read
+  // it, nor leave references behind to be copied twice: whatever happens, the references move to
+  // `copying`, the event is recorded and the slot is marked in flight; the first error is returned.
+  int rc = BT_OK;
+  std::string why;
+  auto note = [&](int code) {
+    if (code != BT_OK && rc == BT_OK) { rc = code; why = bt::last_error_ref(); }
+  };
+  auto copy = [&](void* dst, const void* src, uint64_t n) {
+    if (rc != BT_OK) return;
+    cudaError_t e = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) note(bt::fail(BT_E_CUDA, "cudaMemcpyAsync failed: %s", cudaGetErrorString(e)));
+  };
+  for (const bt::PendingRef& p : pend) note(bt_shm_check(p.seg, p.shm_slot));   // still ours before we read them
   for (size_t ci = 0; ci < s->cols.size(); ++ci) {
     const bt_column& c = s->cols[ci];
     if (by_ref[ci] == n_items && n_items > 0) continue;          // whole column comes from shared memory
-    if (by_ref[ci] > 0) {                                        // mixed: bring the referenced items in first
+    if (by_ref[ci] > 0 && rc == BT_OK) {                         // mixed: bring the referenced items in first
       for (const bt::PendingRef& p : pend)
         if (p.column == (int)ci)
           memcpy(host + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot), p.nbytes);
     }
     const uint64_t nbytes = c.item_bytes * (uint64_t)n_items;
-    if (nbytes)
-      BT_CUDA_TRY(cudaMemcpyAsync(dev + c.slot_off, host + c.slot_off, nbytes, cudaMemcpyHostToDevice, st));
+    if (nbytes) copy(dev + c.slot_off, host + c.slot_off, nbytes);
   }
   std::vector<bt::PendingRef>& fly = r->copying[slot];
   for (const bt::PendingRef& p : pend) {
     const bt_column& c = s->cols[p.column];
     if (by_ref[p.column] == n_items)
-      BT_CUDA_TRY(cudaMemcpyAsync(dev + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot),
-                                  p.nbytes, cudaMemcpyHostToDevice, st));
+      copy(dev + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot), p.nbytes);
     fly.push_back(p);   // (mixed columns were copied above; their slots are released with the rest)
   }
   pend.clear();
-  BT_CUDA_TRY(cudaEventRecord(r->done[slot], st));
-  r->in_flight[slot] = 1;
-  return BT_OK;
+  cudaError_t e = cudaEventRecord(r->done[slot], st);
+  if (e != cudaSuccess) {
+    note(bt::fail(BT_E_CUDA, "cudaEventRecord failed: %s", cudaGetErrorString(e)));
+    cudaStreamSynchronize(st);   // no event to wait on later: make sure nothing still reads the slot
+  }
+  r->in_flight[slot] = (e == cudaSuccess);
+  if (rc != BT_OK) bt::last_error_ref() = why;
+  return rc;
 }
 
 int bt_ring_reap(bt_ring* r) {
@@ -226,7 +256,8 @@ int bt_ring_reap(bt_ring* r) {
     cudaError_t e = cudaEventQuery(r->done[i]);
     if (e == cudaSuccess) {
       r->in_flight[i] = 0;
-      release_refs(r->copying[i]);
+      int rc = release_refs(r->copying[i]);
+      if (rc != BT_OK) return rc;
     } else if (e != cudaErrorNotReady) {
       return bt::fail(BT_E_CUDA, "cudaEventQuery failed: %s", cudaGetErrorString(e));
     }

@@ -736,14 +736,20 @@ int place_fields(const bt_schema* s, uint8_t* base, int item, const uint8_t* msg
         int rc = shm_attach_cached(reinterpret_cast<const char*>(msg + fi->payload_off), fi->payload_len,
                                    refs ? device : -1, &seg);
         if (rc != BT_OK) return rc;
-        const int slot = (int)fi->ival;
-        if (slot >= bt_shm_nslots(seg) || c.item_bytes > bt_shm_slot_bytes(seg))
+        // the announced number is a ticket: slot | generation << 16 (shm.cu)
+        if (fi->ival < 0 || fi->ival > 0x7FFFFFFF || (int)(fi->ival & 0xFFFF) >= bt_shm_nslots(seg) ||
+            c.item_bytes > bt_shm_slot_bytes(seg))
           return fail(BT_E_SCHEMA, "field '%s': shared-memory reference out of range", c.key);
+        const int ticket = (int)fi->ival;
+        rc = bt_shm_check(seg, ticket);   // still ours?  (a slot held past the producer's lease is not)
+        if (rc != BT_OK) return rc;
         if (refs) {
-          refs->push_back(PendingRef{seg, slot, (int)ci, item, c.item_bytes});
+          refs->push_back(PendingRef{seg, ticket, (int)ci, item, c.item_bytes});
         } else {
-          memcpy(dst, bt_shm_slot_ptr(seg, slot), c.item_bytes);
-          bt_shm_release(seg, slot);
+          memcpy(dst, bt_shm_slot_ptr(seg, ticket), c.item_bytes);
+          rc = bt_shm_check(seg, ticket);  // and it stayed ours while we copied
+          if (rc != BT_OK) return rc;
+          bt_shm_release(seg, ticket);
         }
         break;
       }

@@ -3,10 +3,14 @@
 //
 // Segment layout (POSIX shm, name "/btshm_..."):
 //   [Header 64 B][SlotState 64 B x nslots][pad to 4096][slot 0][slot 1]...      slots are 4096-aligned
-// A slot is BUSY from the producer's bt_shm_acquire until the consumer's bt_shm_release.  There is
-// one producer per segment, so acquire needs no CAS: it waits for `busy == 0` (acquire load) on the
-// next slot in round-robin order and then owns it.  The consumer page-locks the whole mapping once
-// with cudaHostRegister, after which slots are valid DMA sources for cudaMemcpyAsync.
+// A slot is BUSY from the producer's bt_shm_acquire until the consumer's bt_shm_release.  Its state
+// is one atomic word, (generation << 1) | busy: every acquire bumps the generation by
+// compare-and-swap (several producers may share a segment), and what travels in the message is a
+// *ticket* = slot | generation << 16.  A consumer that still holds a ticket whose slot has been taken
+// back (the lease below) sees the mismatch before and after its copy or DMA and fails loudly instead of
+// delivering another frame's bytes; its late release is a failed CAS, not a second hand-out.  The
+// consumer page-locks the whole mapping once with cudaHostRegister, after which slots are valid DMA
+// sources for cudaMemcpyAsync.
 #include <cuda_runtime.h>
 #include <fcntl.h>
 #include <sys/mman.h>
@@ -16,6 +20,7 @@
 
 #include <atomic>
 #include <cerrno>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -33,16 +38,21 @@ struct Header {
   uint32_t version, nslots;
   uint64_t slot_bytes;
   uint64_t data_off;
-  uint8_t pad[32];
+  std::atomic<uint64_t> lease_ns;  // 0: slots are never taken back from a consumer
+  uint8_t pad[24];
 };
 static_assert(sizeof(Header) == 64, "header is one cache line");
 
 struct SlotState {
-  std::atomic<uint32_t> busy;
+  std::atomic<uint32_t> word;      // (generation << 1) | busy; generation in 1..kGenMask
   uint32_t pad0;
   std::atomic<uint64_t> since_ns;  // CLOCK_MONOTONIC time of the acquire that made it busy
   uint8_t pad[48];
 };
+constexpr uint32_t kSegmentVersion = 2;
+constexpr uint32_t kGenMask = 0x7FFF;          // 15 bits: a ticket fits a non-negative int
+constexpr int kSlotBits = 16;                  // nslots <= 65536
+inline uint32_t next_gen(uint32_t g) { return g >= kGenMask ? 1 : g + 1; }
 static_assert(sizeof(SlotState) == 64, "one cache line per slot");
 
 }  // namespace
@@ -102,7 +112,10 @@ int map_segment(const char* name, bool create, uint64_t slot_bytes, int nslots, 
   s->creator = create;
   if (create) {
     memset(s->base, 0, data_off);
-    s->hdr->version = 1;
+    s->hdr->version = kSegmentVersion;
+    uint64_t lease_ms = 30000;   // see bt_shm_set_lease
+    if (const char* e = getenv("BT_SHM_LEASE_MS")) lease_ms = strtoull(e, nullptr, 10);
+    s->hdr->lease_ns.store(lease_ms * 1000000ull, std::memory_order_relaxed);
     s->hdr->nslots = (uint32_t)nslots;
     s->hdr->slot_bytes = slot_bytes;
     s->hdr->data_off = data_off;
@@ -110,8 +123,13 @@ int map_segment(const char* name, bool create, uint64_t slot_bytes, int nslots, 
     s->hdr->magic = kMagic;
   } else {
     const Header* h = s->hdr;
-    if (h->magic != kMagic || h->version != 1 || h->nslots == 0 ||
-        h->data_off + h->slot_bytes * (uint64_t)h->nslots > bytes) {
+    // every term is bounded before it is used: a crafted header must not make state[i] or a slot
+    // point outside the mapping (nslots <= 65536 keeps the products far from wrapping)
+    bool ok = h->magic == kMagic && h->version == kSegmentVersion && h->nslots != 0 && h->nslots <= 65536 &&
+              h->slot_bytes != 0 && h->slot_bytes <= bytes && h->data_off <= bytes &&
+              h->data_off >= sizeof(Header) + sizeof(SlotState) * (uint64_t)h->nslots;
+    if (ok) ok = h->slot_bytes * (uint64_t)h->nslots <= bytes - h->data_off;
+    if (!ok) {
       munmap(p, bytes);
       delete s;
       return bt::fail(BT_E_IO, "segment %s has an unknown layout", name);
@@ -180,8 +198,9 @@ int bt_shm_close(bt_shm* s) {
 int bt_shm_nslots(const bt_shm* s) { return s ? (int)s->hdr->nslots : bt::fail(BT_E_INVALID, "null segment"); }
 uint64_t bt_shm_slot_bytes(const bt_shm* s) { return s ? s->hdr->slot_bytes : 0; }
 
-void* bt_shm_slot_ptr(bt_shm* s, int slot) {
-  if (!s || slot < 0 || slot >= (int)s->hdr->nslots) {
+void* bt_shm_slot_ptr(bt_shm* s, int ticket) {
+  const int slot = ticket & ((1 << kSlotBits) - 1);
+  if (!s || ticket < 0 || slot >= (int)s->hdr->nslots) {
     bt::fail(BT_E_INVALID, "bt_shm_slot_ptr: bad slot");
     return nullptr;
   }
@@ -194,41 +213,70 @@ static uint64_t now_ns() {
   return (uint64_t)t.tv_sec * 1000000000ull + (uint64_t)t.tv_nsec;
 }
 
-// A slot whose consumer never released it (it exited with the message still queued) is taken back
-// after this long.  Live consumers hold slots for milliseconds.
-static const uint64_t kLeaseNs = 30ull * 1000000000ull;
+int bt_shm_set_lease(bt_shm* s, int64_t lease_ms) {
+  if (!s || lease_ms < 0) return bt::fail(BT_E_INVALID, "bt_shm_set_lease: bad arguments");
+  s->hdr->lease_ns.store((uint64_t)lease_ms * 1000000ull, std::memory_order_relaxed);
+  return BT_OK;
+}
 
-int bt_shm_acquire(bt_shm* s, int timeout_ms, int* slot) {
-  if (!s || !slot) return bt::fail(BT_E_INVALID, "bt_shm_acquire: bad arguments");
+int bt_shm_acquire(bt_shm* s, int timeout_ms, int* ticket) {
+  if (!s || !ticket) return bt::fail(BT_E_INVALID, "bt_shm_acquire: bad arguments");
   const uint32_t n = s->hdr->nslots;
   const uint64_t t0 = now_ns();
   unsigned spins = 0;
   while (true) {
     // first free slot at or after `next`: a slot that is still held does not block the others
     const uint64_t now = now_ns();
+    const uint64_t lease = s->hdr->lease_ns.load(std::memory_order_relaxed);
     for (uint32_t k = 0; k < n; ++k) {
       const uint32_t i = (s->next + k) % n;
       SlotState& st = s->state[i];
-      const bool free_now = st.busy.load(std::memory_order_acquire) == 0;
-      if (free_now || now - st.since_ns.load(std::memory_order_relaxed) > kLeaseNs) {
-        st.since_ns.store(now, std::memory_order_relaxed);
-        st.busy.store(1, std::memory_order_relaxed);
-        s->next = (i + 1) % n;
-        *slot = (int)i;
-        return BT_OK;
-      }
+      uint32_t w = st.word.load(std::memory_order_acquire);
+      // Lossy by design and opt-out (lease 0): a slot held longer than the lease is taken back so that
+      // consumers that died with messages queued cannot starve the producer; the generation bump makes
+      // a consumer that was merely slow notice (bt_shm_check) instead of reading the new frame.
+      const bool expired = (w & 1) && lease != 0 && now - st.since_ns.load(std::memory_order_relaxed) > lease;
+      if ((w & 1) && !expired) continue;
+      const uint32_t gen = next_gen(w >> 1);
+      if (!st.word.compare_exchange_strong(w, (gen << 1) | 1u, std::memory_order_acq_rel)) continue;  // another producer won
+      st.since_ns.store(now, std::memory_order_relaxed);
+      s->next = (i + 1) % n;
+      *ticket = (int)(i | (gen << kSlotBits));
+      return BT_OK;
     }
+    if (timeout_ms == 0) return BT_E_TIMEOUT;   // a poll: no message recorded
     if (++spins < 100) continue;
     struct timespec nap = {0, 20000};  // 20 us
     nanosleep(&nap, nullptr);
-    if (timeout_ms >= 0 && (now_ns() - t0) / 1000000ull > (uint64_t)timeout_ms)
+    if (timeout_ms > 0 && (now_ns() - t0) / 1000000ull > (uint64_t)timeout_ms)
       return bt::fail(BT_E_TIMEOUT, "no free shared-memory slot within %d ms (consumers stalled?)", timeout_ms);
   }
 }
 
-int bt_shm_release(bt_shm* s, int slot) {
-  if (!s || slot < 0 || slot >= (int)s->hdr->nslots) return bt::fail(BT_E_INVALID, "bt_shm_release: bad slot");
-  s->state[slot].busy.store(0, std::memory_order_release);
+int bt_shm_check(const bt_shm* s, int ticket) {
+  const int slot = ticket & ((1 << kSlotBits) - 1);
+  if (!s || ticket < 0 || slot >= (int)s->hdr->nslots) return bt::fail(BT_E_INVALID, "bt_shm_check: bad ticket");
+  const uint32_t gen = (uint32_t)ticket >> kSlotBits;
+  if (gen == 0) return BT_OK;   // a bare slot number: nothing to compare
+  if (s->state[slot].word.load(std::memory_order_acquire) != ((gen << 1) | 1u))
+    return bt::fail(BT_E_IO, "shared-memory slot %d of %s was taken back by its producer (held past the lease) "
+                             "while this consumer was still using it", slot, s->name.c_str());
+  return BT_OK;
+}
+
+int bt_shm_release(bt_shm* s, int ticket) {
+  const int slot = ticket & ((1 << kSlotBits) - 1);
+  if (!s || ticket < 0 || slot >= (int)s->hdr->nslots) return bt::fail(BT_E_INVALID, "bt_shm_release: bad slot");
+  const uint32_t gen = (uint32_t)ticket >> kSlotBits;
+  std::atomic<uint32_t>& word = s->state[slot].word;
+  uint32_t w = word.load(std::memory_order_relaxed);
+  if (gen == 0) {   // a bare slot number (tools, drain): free whatever generation holds it
+    while ((w & 1) && !word.compare_exchange_weak(w, w & ~1u, std::memory_order_release)) {}
+    return BT_OK;
+  }
+  uint32_t expect = (gen << 1) | 1u;
+  if (!word.compare_exchange_strong(expect, gen << 1, std::memory_order_release))
+    return bt::fail(BT_E_IO, "stale release of shared-memory slot %d of %s (taken back by its producer)", slot, s->name.c_str());
   return BT_OK;
 }
 

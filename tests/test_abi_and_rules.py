@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, n), "libbt_b200.so lacks %s" % n
     assert sorted(N.EXPORTS) == sorted(x for x in names if x in N.EXPORTS)
     assert set(names) <= set(N.EXPORTS)
-    assert N.lib.bt_abi_version() == 2
+    assert N.lib.bt_abi_version() == 3
     out = subprocess.run(["nm", "-D", "--defined-only", str(N.LIB_PATH)], capture_output=True, text=True).stdout
     exported = set(re.findall(r" T (bt_[a-z0-9_]+)", out))
     assert set(names) <= exported

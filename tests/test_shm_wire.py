@@ -27,13 +27,13 @@ def test_segment_put_fetch_and_backpressure():
     assert seg.slot_bytes == 4096       # rounded to pages
     arrs = [np.arange(i, i + 200, dtype=np.float32).reshape(10, 20) for i in range(3)]
     marks = [seg.put(a) for a in arrs]
-    assert [m[2] for m in marks] == [0, 1, 2] and marks[0][3] == "<f4" and marks[0][4] == (10, 20)
+    assert [m[2] & 0xFFFF for m in marks] == [0, 1, 2] and all(m[2] >> 16 for m in marks) and marks[0][3] == "<f4" and marks[0][4] == (10, 20)
     with pytest.raises(N.NativeError) as e:   # every slot is held by a consumer that has not released
         seg.put(arrs[0], timeout_ms=50)
     assert e.value.code == N.BT_E_TIMEOUT
     np.testing.assert_array_equal(shm.fetch(marks[0]), arrs[0])      # releases slot 0
     m = seg.put(arrs[2], timeout_ms=50)
-    assert m[2] == 0
+    assert m[2] & 0xFFFF == 0 and m[2] != marks[0][2]          # same slot, next generation
     for mk, a in ((marks[1], arrs[1]), (marks[2], arrs[2]), (m, arrs[2])):
         np.testing.assert_array_equal(shm.fetch(mk), a)
     with pytest.raises(ValueError):
@@ -51,7 +51,7 @@ def test_scanner_and_schema_understand_references():
     blobs = [pickle.dumps({"btid": 1, "image": seg.put(f), "frameid": i, "xy": np.full((2, 2), float(i))}, protocol=3)
              for i, f in enumerate(frames)]
     f = {x.key.decode(): x for x in N.scan_message(blobs[1])}
-    assert f["image"].kind == N.BT_KIND_SHMREF and f["image"].dtype == N.BT_U8 and f["image"].ival == 1
+    assert f["image"].kind == N.BT_KIND_SHMREF and f["image"].dtype == N.BT_U8 and f["image"].ival & 0xFFFF == 1
     assert [f["image"].shape[d] for d in range(3)] == [6, 10, 4]
     assert bytes(blobs[1][f["image"].payload_off:f["image"].payload_off + f["image"].payload_len]).decode() == seg.name
     sch = Schema.from_message(blobs[0], 3)
