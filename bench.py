@@ -9,17 +9,23 @@ batch 8, fused flip + gamma 2.2 + normalise + NHWC->NCHW to fp32 on one B200.
 A step is one pass of the hot path over one batch of 8 frames.
 
 Printed JSON line (rank 0):
-  value      images/s of the device leg: K launches of the fused kernel K1 over batches already
-             resident in HBM (rotating over distinct batches so the working set exceeds L2),
-             replayed from a CUDA graph, timed with CUDA events, max over ranks.
-  e2e        images/s through the public API (btt.DeviceLoader over btt.RemoteIterableDataset)
-             with HOST buffers: ZMQ receive, framing, pinned staging, H2D copy, K1 and a D2H read of
-             the batch statistics are all inside the timed region.
+  value      images/s of the device leg: the fused kernel K1 over batches already resident in HBM
+             (rotating over distinct batches so the working set exceeds L2), replayed from CUDA graphs
+             only, timed with CUDA events over a window of >= 20 ms, max over ranks.
+  e2e        images/s through the public API (btt.DeviceLoader over btt.RemoteIterableDataset) with HOST
+             buffers: socket receive, framing, pinned staging, H2D copy, K1 and a D2H read of the batch
+             statistics are all inside the timed region; after warm-up the batches that were already
+             produced are discarded and at least `steps` batches AND 2 s are timed.  A sampled batch is
+             checked against the publishers' frames outside the timed region (e2e_check).
   roofline   K1 algorithmic bytes per launch (H*W*C*(1 + 4) per image = 20 B/pixel)
-             / average launch duration, against the measured HBM copy peak.
-  cpu_baseline  the oracle port of the reference's CPU path (decode + item_transform + default_collate
-             under torch DataLoader workers) timed on this box's host cores on a bounded sample.
-With --impl reference only that CPU path is run and reported (rank 0 alone under torchrun).
+             / average launch duration, against the measured HBM copy peak; `single_launch` is the same
+             kernel on one stream, `e2e_kernel` the statistics variant + fold the e2e path runs.
+  configs    the other BASELINE.json shapes end to end (C1 replay, C3 1080p + depth + projection,
+             C4 1024^2 batch 64, C5 128^2 batch 1024), with their kernel times.
+  cpu_baseline  the reference's CPU path timed on this box's host cores (see --impl reference).
+With --impl reference only the reference's CPU path is run: its own btt.RemoteIterableDataset (the
+unmodified files, copied to oracle/_ref by build(); the oracle port if they are absent) + the example
+item_transforms + default_collate under torch DataLoader workers on every host core.
 """
 import argparse
 import json
@@ -27,24 +33,31 @@ import os
 import signal
 import socket
 import statistics
+import shutil
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
 PKG = ROOT / "pytorch-blender_b200"
-for _p in (str(ROOT), str(PKG)):
-    if _p not in sys.path:
-        sys.path.insert(0, _p)
+REF = ROOT / "oracle" / "_ref"
 
 H, W, C, BATCH, PUBLISHERS, CONFIG = 480, 640, 4, 8, 5, 2
 GAMMA, MEAN, STD = 2.2, 127.5, 127.5
 WORKLOAD = "C2: 5 synthetic ZMQ publishers, 640x480 RGBA uint8 + bbox, batch 8, flip+gamma2.2+normalise+NCHW fp32"
 METRIC = "images/sec into device tensors (640x480 RGBA, batch 8)"
-DEVICE_STREAMS = 4  # independent batches in flight in the device leg (DeviceLoader default: up to 4 receivers)
+CONFIG_KEYS = {"workload": WORKLOAD, "batch": BATCH, "publishers": PUBLISHERS}   # identical in both arms
+DEVICE_STREAMS = 4  # independent batches in flight in the device leg (one stream per receiver in the pipeline)
 ROTATE = 8  # distinct resident batches: 8 x (9.8 MB in + 39.3 MB out) = 393 MB > 126 MB L2
+
+
+def _use_product():
+    for p in (str(ROOT), str(PKG)):
+        if p not in sys.path:
+            sys.path.insert(0, p)
 
 
 def free_port():
@@ -164,11 +177,12 @@ class ClockSampler:
 def measured_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the headline kernel, from the committed
     ncu --set full capture (profiles/); None if no capture is there."""
-    f = ROOT / "profiles" / "r1_k1_traffic.json"
-    try:
-        return float(json.loads(f.read_text())["dram_bytes_read_plus_write_per_launch"])
-    except Exception:
-        return None
+    for name in ("r2_k1_traffic.json", "r1_k1_traffic.json"):
+        try:
+            return float(json.loads((ROOT / "profiles" / name).read_text())["dram_bytes_read_plus_write_per_launch"])
+        except Exception:
+            continue
+    return None
 
 
 def measured_peaks():
@@ -181,9 +195,18 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def rank_cpus(local_rank, world):
+    """The host cores of this rank: the process's allowed cpus split into `world` equal, disjoint runs
+    (one process per GPU, each with its own receivers, publishers and consumer thread on its own cores)."""
+    cpus = sorted(os.sched_getaffinity(0))
+    per = max(1, len(cpus) // max(world, 1))
+    mine = cpus[local_rank * per:(local_rank + 1) * per] if world > 1 else cpus
+    return mine or cpus
+
+
 # --------------------------------------------------------------------------------------------
-# CPU path of the reference (oracle port): the cpu_baseline leg and the --impl reference arm.
-# This is the only place bench.py touches oracle/.
+# CPU path of the reference: the cpu_baseline leg and the --impl reference arm.
+# This is the only place bench.py touches oracle/ (and it never imports the product).
 # --------------------------------------------------------------------------------------------
 def _cpu_transform(item):
     from oracle import preprocess as opre
@@ -198,34 +221,50 @@ def _worker_init(_):
     torch.set_num_threads(1)
 
 
-def run_cpu_reference(steps, warmup, workers, max_seconds=None, check_shape=True):
-    """Reference CPU path on this box: synthetic publishers -> (oracle) RemoteIterableDataset port
-    -> item_transform -> default_collate in `workers` DataLoader processes.  Returns
-    (images/s, steps timed, seconds)."""
-    from torch.utils.data import DataLoader
+def _reference_dataset(addrs, max_items):
+    """(dataset, kind): the reference's own RemoteIterableDataset when build() has copied the unmodified
+    package to oracle/_ref ("reference"), else the oracle's restatement of it ("port")."""
+    if (REF / "blendtorch" / "btt" / "dataset.py").exists():
+        if str(REF) not in sys.path:
+            sys.path.insert(0, str(REF))
+        from blendtorch import btt as ref_btt
+        assert str(REF) in ref_btt.__file__, "the product package shadows oracle/_ref"
+        return ref_btt.RemoteIterableDataset(addrs, max_items=max_items, item_transform=_cpu_transform,
+                                             timeoutms=60000), "reference"
     from oracle import stream
+    return stream.torch_stream_dataset(addrs, max_items=max_items, item_transform=_cpu_transform, timeoutms=60000), "port"
+
+
+def run_cpu_reference(steps, warmup, workers, min_seconds=5.0, max_seconds=30.0):
+    """Reference CPU path on this box: synthetic publishers -> RemoteIterableDataset -> item_transform ->
+    default_collate in `workers` DataLoader processes (prefetch_factor 2, torch's default and what
+    benchmarks/benchmark.py:26-28 runs with).  After warm-up, workers x prefetch_factor batches are
+    discarded (they were made before the clock starts); then at least `steps` batches and `min_seconds`
+    are timed.  Returns (images/s, batches timed, seconds, kind)."""
+    if str(ROOT) not in sys.path:
+        sys.path.insert(0, str(ROOT))
+    from torch.utils.data import DataLoader
     addrs, procs = spawn_publishers("oracle.synth", PUBLISHERS, tag="ref")
     try:
-        total_batches = steps + warmup
-        per_worker = -(-total_batches // max(workers, 1)) + 2
-        ds = stream.torch_stream_dataset(addrs, max_items=per_worker * BATCH * max(workers, 1),
-                                         item_transform=(lambda it: _cpu_transform(it)), timeoutms=60000)
+        ds, kind = _reference_dataset(addrs, max_items=10 ** 8)
+        prefetch = 2
         dl = DataLoader(ds, batch_size=BATCH, num_workers=workers, worker_init_fn=_worker_init,
-                        persistent_workers=False, prefetch_factor=4 if workers else None)
+                        persistent_workers=False, prefetch_factor=prefetch if workers else None)
         it = iter(dl)
-        for _ in range(warmup):
+        for _ in range(warmup + (workers * prefetch if workers else 0)):
             next(it)
         t0 = time.perf_counter()
         done = 0
-        for _ in range(steps):
+        while True:
             b = next(it)
-            assert not check_shape or b["image"].shape == (BATCH, C, H, W)
+            assert b["image"].shape == (BATCH, C, H, W)
             done += 1
-            if max_seconds and time.perf_counter() - t0 > max_seconds:
+            dt = time.perf_counter() - t0
+            if (done >= steps and dt >= min_seconds) or dt >= max_seconds:
                 break
         dt = time.perf_counter() - t0
         del it
-        return done * BATCH / dt, done, dt
+        return done * BATCH / dt, done, dt, kind
     finally:
         stop_publishers(procs)
 
@@ -234,18 +273,22 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    cores = os.cpu_count() or 1
+    cores = len(os.sched_getaffinity(0))
     workers = max(1, min(cores, 64))  # all host threads: measured fastest (profiles/r1_cpu_baseline_sweep.jsonl)
-    ips, done, dt = run_cpu_reference(args.steps, args.warmup, workers)
+    ips, done, dt, kind = run_cpu_reference(args.steps, args.warmup, workers, min_seconds=args.cpu_seconds)
+    what = ("the reference's own btt.RemoteIterableDataset (unmodified files in oracle/_ref)" if kind == "reference"
+            else "oracle port of btt.RemoteIterableDataset")
     line = {
         "impl": "reference", "metric": METRIC, "value": ips, "unit": "images/s", "n_gpus": args.gpus,
-        "steps": done, "warmup": args.warmup, "ms_per_step": dt / max(done, 1) * 1e3,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / max(done, 1) * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "batch": BATCH, "publishers": PUBLISHERS,
-                   "transform": "flipud + gamma_correct(2.2) + (x-127.5)/127.5 + CHW, default_collate"},
-        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": workers, "kind": "port",
-                         "sample": "%d batches of %d through %d DataLoader workers (%d host cpus); oracle port of "
-                                   "btt.RemoteIterableDataset + example item_transforms" % (done, BATCH, workers, cores)},
+        "config": dict(CONFIG_KEYS),
+        "config_detail": {"transform": "flipud + gamma_correct(2.2) + (x-127.5)/127.5 + CHW, default_collate",
+                          "workers": workers, "prefetch_factor": 2, "timed_steps": done, "window_s": dt},
+        "timed_steps": done,
+        "cpu_baseline": {"value": ips, "unit": "images/s", "cores": workers, "kind": kind,
+                         "sample": "%d batches of %d in %.1f s through %d DataLoader workers (%d host cpus); %s + "
+                                   "flipud/gamma/normalise item_transform + default_collate" % (done, BATCH, dt, workers, cores, what)},
         "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -256,300 +299,150 @@ def reference_arm(args):
 # --------------------------------------------------------------------------------------------
 # Our arm
 # --------------------------------------------------------------------------------------------
-def device_leg(torch, btt, dev, steps, warmup, spec, sampler, n_streams=4):
-    """K1 over HBM-resident batches.  Returns (seconds for `steps` launches, bytes per launch)."""
+def _graph_of(torch, stream, enqueue):
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=stream):
+        enqueue()
+    return g
+
+
+def _time_graphs(torch, stream, graphs, min_ms=20.0, sampler=None):
+    """Replay the graph sequence R times so that the CUDA-event window is >= min_ms; (seconds, R)."""
+    for g in graphs:
+        g.replay()
+    stream.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for g in graphs:
+        g.replay()
+    e1.record(stream)
+    e1.synchronize()
+    once = max(e0.elapsed_time(e1), 1e-3)
+    reps = max(1, int(min_ms / once) + 1)
+    if sampler:
+        sampler.active = True
+    e0.record(stream)
+    for _ in range(reps):
+        for g in graphs:
+            g.replay()
+    e1.record(stream)
+    e1.synchronize()
+    if sampler:
+        sampler.active = False
+    return e0.elapsed_time(e1) * 1e-3, reps
+
+
+def device_leg(torch, btt, dev, steps, warmup, sampler):
+    """K1 over HBM-resident batches, no eager launch inside any timed region.  Returns a dict:
+    overlapped (DEVICE_STREAMS streams, the pipeline's shape: `value`), single (one stream, back to back),
+    e2e_kernel (statistics variant + fold, one stream: what the e2e path launches per batch)."""
     g = torch.Generator(device=dev)
     g.manual_seed(2000)
     srcs = [torch.randint(0, 256, (BATCH, H, W, C), dtype=torch.uint8, device=dev, generator=g) for _ in range(ROTATE)]
     outs = [torch.empty((BATCH, C, H, W), dtype=torch.float32, device=dev) for _ in range(ROTATE)]
-    # One stream per receiver, as in the pipeline (every DeviceLoader receiver owns a stream): the
-    # graph forks into `streams` branches so that launches of independent batches overlap their
-    # ramp-up and tail exactly as they do end to end.
-    streams = [torch.cuda.Stream(dev) for _ in range(max(1, n_streams))]
+    spec = btt.Preprocess(key="image", flip=True, gamma=GAMMA, mean=MEAN, std=STD)
+    spec_stats = btt.Preprocess(key="image", flip=True, gamma=GAMMA, mean=MEAN, std=STD, stats=True)
+    streams = [torch.cuda.Stream(dev) for _ in range(DEVICE_STREAMS)]
     stream = streams[0]
-    launches_per_graph = ROTATE
+    stats_out = [torch.empty((C, 2), dtype=torch.float64, device=dev) for _ in range(ROTATE)]
+    scratch = torch.empty(4 << 20, dtype=torch.uint8, device=dev)
 
-    def enqueue_round():
-        if len(streams) > 1:
+    def fan(n):
+        def enqueue():
             fork = torch.cuda.Event()
             fork.record(stream)
             for s in streams[1:]:
                 s.wait_event(fork)
-        for i in range(launches_per_graph):
-            btt.preprocess_images(srcs[i], spec, out=outs[i], stream=streams[i % len(streams)])
-        for s in streams[1:]:
-            join = torch.cuda.Event()
-            join.record(s)
-            stream.wait_event(join)
+            for i in range(n):
+                btt.preprocess_images(srcs[i % ROTATE], spec, out=outs[i % ROTATE], stream=streams[i % len(streams)])
+            for s in streams[1:]:
+                join = torch.cuda.Event()
+                join.record(s)
+                stream.wait_event(join)
+        return enqueue
 
+    def chain(n, sp, with_stats):
+        def enqueue():
+            for i in range(n):
+                if with_stats:
+                    btt.preprocess_images(srcs[i % ROTATE], sp, out=outs[i % ROTATE], stream=stream,
+                                          stats_out=stats_out[i % ROTATE], _scratch=scratch)
+                else:
+                    btt.preprocess_images(srcs[i % ROTATE], sp, out=outs[i % ROTATE], stream=stream)
+        return enqueue
+
+    out = {}
     with torch.cuda.stream(stream):
         for i in range(max(warmup, 3)):
             btt.preprocess_images(srcs[i % ROTATE], spec, out=outs[i % ROTATE], stream=stream)
+            btt.preprocess_images(srcs[i % ROTATE], spec_stats, out=outs[i % ROTATE], stream=stream,
+                                  stats_out=stats_out[i % ROTATE], _scratch=scratch)
         stream.synchronize()
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph, stream=stream):
-            enqueue_round()
-        graph.replay()
-        stream.synchronize()
-        n_replays, tail = divmod(steps, launches_per_graph)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        sampler.active = True
-        e0.record(stream)
-        for _ in range(n_replays):
-            graph.replay()
-        for i in range(tail):
-            btt.preprocess_images(srcs[i], spec, out=outs[i], stream=stream)
-        e1.record(stream)
-        e1.synchronize()
-        sampler.active = False
-    sec = e0.elapsed_time(e1) * 1e-3
-    algo_bytes = BATCH * H * W * C * (1 + 4)
-    return sec, algo_bytes
+        # `steps` launches = whole rounds of ROTATE plus a tail, both as graphs
+        n_round, tail = divmod(steps, ROTATE)
+        graphs = [_graph_of(torch, stream, fan(ROTATE))] * n_round
+        if tail:
+            graphs.append(_graph_of(torch, stream, fan(tail)))
+        sec, reps = _time_graphs(torch, stream, graphs, sampler=sampler)
+        out["overlapped"] = {"sec_per_launch": sec / (reps * steps), "launches_timed": reps * steps, "replays": reps,
+                             "window_ms": sec * 1e3}
+        sec, reps = _time_graphs(torch, stream, [_graph_of(torch, stream, chain(ROTATE, spec, False))], sampler=sampler)
+        out["single"] = {"sec_per_launch": sec / (reps * ROTATE), "launches_timed": reps * ROTATE, "window_ms": sec * 1e3}
+        sec, reps = _time_graphs(torch, stream, [_graph_of(torch, stream, chain(ROTATE, spec_stats, True))], sampler=sampler)
+        out["e2e_kernel"] = {"sec_per_launch": sec / (reps * ROTATE), "launches_timed": reps * ROTATE, "window_ms": sec * 1e3}
+    out["algo_bytes"] = BATCH * H * W * C * (1 + 4)
+    return out
 
 
-def large_batch_probe(torch, btt, dev, spec):
-    """Same kernel on BASELINE config 4's per-GPU batch (64 x 1024x1024 RGBA), where launch ramp and
-    tail are amortised: reported beside the headline roofline, not instead of it."""
-    B2, H2, W2 = 64, 1024, 1024
+def kernel_times(torch, btt, dev, h, w, batch, depth=False, corners=0):
+    """CUDA-event time per launch of the kernels a config's batch runs (K1 with statistics + fold, the
+    depth flip, K2), each over inputs larger than L2 or rotated so, from graphs."""
+    stream = torch.cuda.Stream(dev)
+    res = {}
+    frame_bytes = batch * h * w * 4
+    rot = max(2, min(8, -(-(200 << 20) // (frame_bytes * 5))))
     g = torch.Generator(device=dev)
-    g.manual_seed(4000)
-    src = torch.randint(0, 256, (B2, H2, W2, C), dtype=torch.uint8, device=dev, generator=g)
-    out = torch.empty((B2, C, H2, W2), dtype=torch.float32, device=dev)
-    for _ in range(3):
-        btt.preprocess_images(src, spec, out=out)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    reps = 20
-    e0.record()
-    for _ in range(reps):
-        btt.preprocess_images(src, spec, out=out)
-    e1.record()
-    e1.synchronize()
-    sec = e0.elapsed_time(e1) * 1e-3 / reps
-    return B2 * H2 * W2 * C * 5 / sec / 1e9, sec
+    g.manual_seed(7)
+    with torch.cuda.stream(stream):
+        srcs = [torch.randint(0, 256, (batch, h, w, 4), dtype=torch.uint8, device=dev, generator=g) for _ in range(rot)]
+        outs = [torch.empty((batch, 4, h, w), dtype=torch.float32, device=dev) for _ in range(rot)]
+        st = [torch.empty((4, 2), dtype=torch.float64, device=dev) for _ in range(rot)]
+        spec = btt.Preprocess(flip=True, gamma=GAMMA, mean=MEAN, std=STD, stats=True)
+        scratch = torch.empty(8 << 20, dtype=torch.uint8, device=dev)
 
+        def k1():
+            for i in range(rot):
+                btt.preprocess_images(srcs[i], spec, out=outs[i], stream=stream, stats_out=st[i], _scratch=scratch)
+        k1()
+        stream.synchronize()
+        sec, reps = _time_graphs(torch, stream, [_graph_of(torch, stream, k1)], min_ms=10.0)
+        t = sec / (reps * rot)
+        res["k1_stats_us"] = t * 1e6
+        res["k1_gbs"] = frame_bytes * 5 / t / 1e9
+        del srcs, outs
+        if depth:
+            d_in = [torch.rand((batch, h, w), dtype=torch.float32, device=dev) for _ in range(2)]
+            d_out = [torch.empty_like(d_in[0]) for _ in range(2)]
 
-def e2e_leg(torch, btt, dev, steps, warmup, sampler, transport, receivers, io_threads=1, shm_slots=0, rx="auto",
-            raw_parts=False):
-    """Public API with host buffers: publishers -> DeviceLoader -> device batch (+ stats read back)."""
-    addrs, procs = spawn_publishers("blendtorch.btt.synthetic", PUBLISHERS, transport, tag="r%s" % os.environ.get("RANK", "0"),
-                                    extra=(("--shm-slots", str(shm_slots)) if shm_slots else ()) +
-                                          (("--raw-parts",) if raw_parts else ()))
-    try:
-        total = (steps + warmup) * BATCH
-        per_recv = -(-(steps + warmup) // receivers) * BATCH
-        ds = btt.RemoteIterableDataset(addrs, max_items=per_recv * receivers + 0, timeoutms=60000)
-        spec = btt.Preprocess(key="image", flip=True, gamma=GAMMA, mean=MEAN, std=STD, stats=True)
-        dl = btt.DeviceLoader(ds, batch_size=BATCH, device=dev, preprocess=spec, num_receivers=receivers,
-                              ring_depth=4, prefetch=4, io_threads=io_threads, transport=rx)
-        it = iter(dl)
-        h2d = d2h = 0
-        for _ in range(warmup):
-            b = next(it)
-            b["image_stats"].cpu()
-        torch.cuda.synchronize(dev)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        sampler.active = True
-        t0 = time.perf_counter()
-        e0.record()
-        images = 0
-        stamps = [t0]
-        for _ in range(steps):
-            b = next(it)
-            st = b["image_stats"].cpu()          # D2H read of the step's result
-            images += b["image"].shape[0]
-            stamps.append(time.perf_counter())
-        e1.record()
-        e1.synchronize()
-        wall = time.perf_counter() - t0
-        sampler.active = False
-        sec = e0.elapsed_time(e1) * 1e-3
-        h2d = sum(v.numel() * v.element_size() for k, v in b.items()
-                  if isinstance(v, torch.Tensor) and k in ("btid", "frameid", "bbox")) + BATCH * H * W * C
-        d2h = st.numel() * st.element_size()
-        it.close() if hasattr(it, "close") else None
-        del it
-        _ = total
-        # spread of the rate over the run: images/s in consecutive windows of 20 batches
-        win = 20
-        rates = sorted(win * BATCH / (stamps[i + win] - stamps[i]) for i in range(0, len(stamps) - win, win)
-                       if stamps[i + win] > stamps[i])
-        e2e_leg.last_spread = ({"window_batches": win, "p10": rates[len(rates) // 10], "p50": rates[len(rates) // 2],
-                                "p90": rates[(len(rates) * 9) // 10]} if rates else None)
-        return images, max(sec, wall), h2d, d2h
-    finally:
-        stop_publishers(procs)
-
-
-def ours(args):
-    import torch
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL announces its version on stdout at the first collective; stdout is reserved for the one
-        # JSON line, so send everything to stderr until the communicator is up.
-        sys.stdout.flush()
-        saved_stdout = os.dup(1)
-        os.dup2(2, 1)
-        try:
-            dist.init_process_group("nccl", device_id=dev)
-            dist.barrier()
-            torch.cuda.synchronize(dev)
-        finally:
-            sys.stdout.flush()
-            os.dup2(saved_stdout, 1)
-            os.close(saved_stdout)
-    import importlib.util
-    spec_ = importlib.util.spec_from_file_location("bt_build_native", PKG / "build_native.py")
-    mod = importlib.util.module_from_spec(spec_)
-    spec_.loader.exec_module(mod)
-    if not mod.LIB.exists():
-        mod.build()
-    from blendtorch import btt
-    from blendtorch.btt import native as N
-    import ctypes
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    def max_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
-
-    sampler = ClockSampler(local)
-    h2d_gbs = ctypes.c_double(0.0)
-    N.check(N.lib.bt_measure_h2d(local, 64 << 20, 20, ctypes.byref(h2d_gbs)))
-
-    spec = btt.Preprocess(key="image", flip=True, gamma=GAMMA, mean=MEAN, std=STD)
-    barrier()
-    sec, algo_bytes = device_leg(torch, btt, dev, args.steps, args.warmup, spec, sampler, DEVICE_STREAMS)
-    barrier()
-    sec = max_over_ranks(sec)
-    value = world * args.steps * BATCH / sec
-    achieved = algo_bytes * args.steps / (sec if world == 1 else sec) / 1e9
-    large_gbs, large_sec = large_batch_probe(torch, btt, dev, spec) if rank == 0 else (0.0, 0.0)
-
-    barrier()
-    images, e2e_sec, h2d, d2h = e2e_leg(torch, btt, dev, args.steps, args.warmup, sampler, args.transport, args.receivers)
-    barrier()
-    e2e_spread = getattr(e2e_leg, "last_spread", None)
-    e2e_sec = max_over_ranks(e2e_sec)
-    images = sum_over_ranks(images)
-    e2e_value = images / e2e_sec
-    # same leg with the publishers bound to ipc:// endpoints (the reference's launcher takes any ZMQ proto)
-    barrier()
-    ipc_images, ipc_sec, _, _ = e2e_leg(torch, btt, dev, args.steps, args.warmup, sampler, "ipc", args.receivers)
-    barrier()
-    ipc_value = sum_over_ranks(ipc_images) / max_over_ranks(ipc_sec)
-    # same leg over the opt-in shared-memory wire (payload by DMA from the producers' segments)
-    barrier()
-    shm_images, shm_sec, _, _ = e2e_leg(torch, btt, dev, args.steps, args.warmup, sampler, args.transport,
-                                        args.shm_receivers, shm_slots=args.shm_slots)
-    barrier()
-    shm_sec = max_over_ranks(shm_sec)
-    shm_value = sum_over_ranks(shm_images) / shm_sec
-    clocks = sampler.report()
-
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cores = os.cpu_count() or 1
-        workers = max(1, min(cores, 64))  # all host threads: measured fastest (profiles/r1_cpu_baseline_sweep.jsonl)
-        ips, done, dt = run_cpu_reference(steps=100000, warmup=2, workers=workers, max_seconds=15.0)
-        cpu = {"value": ips, "unit": "images/s", "cores": workers, "kind": "port",
-               "sample": "%d batches of %d in %.1f s through %d DataLoader workers (%d host cpus); oracle port of "
-                         "btt.RemoteIterableDataset + flipud/gamma/normalise item_transform + default_collate"
-                         % (done, BATCH, dt, workers, cores)}
-    if rank == 0:
-        peak, peak_src = measured_peaks()
-        h2d_bytes_img = H * W * C
-        line = {
-            "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch": BATCH, "publishers": PUBLISHERS,
-                       "l2": "device leg rotates over %d distinct resident batches (%.0f MB working set > 126 MB L2), "
-                             "launches replayed from a CUDA graph over %d streams (the pipeline runs one stream per receiver)"
-                             % (ROTATE, ROTATE * BATCH * H * W * C * 5 / 1e6, DEVICE_STREAMS),
-                       "e2e_transport": args.transport, "e2e_receivers": args.receivers,
-                       "e2e_receiver": "direct ZMTP endpoint (bt_pull_*), unmodified PUSH publishers",
-                       "parallelism": "dp%d, publishers sharded per GPU, no collective" % world},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": measured_traffic(), "peak_source": peak_src,
-                         "traffic_note": "ncu, cold L2: 9.85 MB read (= algorithmic 9.83 MB) + <0.2 MB written back inside the "
-                                         "kernel; the 39.3 MB of fp32 output of a batch-8 launch are absorbed by the 126 MB L2 "
-                                         "and written back after it (C4-size launches write through: see profiles/)",
-                         "kernel": "k1_planar<float,4,4,1> (C,PPT,UNROLL: one 4-pixel unit per thread at this batch size)", "algorithmic_bytes_per_launch": algo_bytes,
-                         "frac_of_nominal_8TBs": achieved / 8000.0,
-                         "large_batch": {"workload": "C4 per-GPU batch: 64 x 1024x1024 RGBA -> fp32 NCHW",
-                                         "achieved": large_gbs, "frac": large_gbs / peak, "ms": large_sec * 1e3}},
-            "e2e": {"value": e2e_value, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "gbs_h2d": e2e_value * h2d_bytes_img / 1e9 / world, "pcie_h2d_measured_gbs": h2d_gbs.value,
-                    "rank0_images_per_s_spread": e2e_spread,
-                    "frac_of_pcie_h2d": e2e_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value},
-            "e2e_ipc": {"value": ipc_value, "unit": "images/s", "gbs_h2d": ipc_value * h2d_bytes_img / 1e9 / world,
-                        "frac_of_pcie_h2d": ipc_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value,
-                        "note": "as e2e, publishers bound to ipc:// instead of tcp://"},
-            "e2e_shm_wire": {"value": shm_value, "unit": "images/s", "gbs_h2d": shm_value * h2d_bytes_img / 1e9 / world,
-                             "frac_of_pcie_h2d": shm_value * h2d_bytes_img / 1e9 / world / h2d_gbs.value,
-                             "note": "opt-in wire for co-located producers (DataPublisher(shm_slots=%d)): payload goes "
-                                     "producer -> shared memory -> DMA, no consumer-side CPU copy; not the reference's "
-                                     "pickle wire, reported beside e2e, not instead of it" % args.shm_slots,
-                             "receivers": args.shm_receivers},
-            "gpu_launches": args.steps,
-            # e2e batches carry statistics (the step's result that is read back): K1 + the fold kernel of its rows
-            "gpu_launches_e2e": 2 * args.steps,
-            "clocks": clocks,
-            "cpu_baseline": cpu,
-            "host": {"cpus": os.cpu_count()},
-        }
-        print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
-    return 0
-
-
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=2000)
-    ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--transport", default="tcp", choices=["tcp", "ipc"])
-    ap.add_argument("--receivers", type=int, default=0, help="receiver threads per GPU (0 = by host cores)")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--shm-slots", type=int, default=32)
-    ap.add_argument("--shm-receivers", type=int, default=2)
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3)
-    if args.receivers <= 0:
-        # receiver threads per GPU: 4 where the host has cores to spare, fewer when N GPUs share few
-        # cores with their N x 5 publisher processes
-        n = max(1, int(os.environ.get("WORLD_SIZE", args.gpus)))
-        spare = (os.cpu_count() or 1) - PUBLISHERS * n
-        args.receivers = min(8, max(1, spare // n))   # direct receiver: one thread per receiver
-    args.shm_receivers = min(args.shm_receivers, args.receivers)
-    if args.impl == "reference":
-        return reference_arm(args)
-    return ours(args)
-
-
-if __name__ == "__main__":
-    sys.exit(main())
+            def fl():
+                for i in range(2):
+                    btt.flip_rows(d_in[i], out=d_out[i], stream=stream)
+            fl()
+            stream.synchronize()
+            sec, reps = _time_graphs(torch, stream, [_graph_of(torch, stream, fl)], min_ms=10.0)
+            res["flip_us"] = sec / (reps * 2) * 1e6
+            res["flip_gbs"] = batch * h * w * 8 / (sec / (reps * 2)) / 1e9
+            del d_in, d_out
+        if corners:
+            cam = btt.Camera.from_lens((h, w), lens=35.0, distance=0.0, device=dev)
+            pts = torch.rand((batch, corners, 3), dtype=torch.float64, device=dev) * 4 + torch.tensor([0, 0, 6.0], device=dev)
+            cam.bbox_world_to_pixel_boxes(pts, 8)
+            stream.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(50):
+                cam.bbox_world_to_pixel_boxes(pts, 8)
+            e1.record(stream)
+            e1.synchronize()
+            res["k2_us_eager"] = e0.elapsed_time(e1) * 1e3 / 50   # launched from Python: host-paced
+    return res
