@@ -553,11 +553,12 @@ def stream_leg(ctx, cfg, transport, receivers, senders, shm_slots=0, min_seconds
         for _ in range(prefetch + receivers):        # produced before the clock starts: not ours to count
             next(it)
         torch.cuda.synchronize(ctx["dev"])
+        before = dict(dl.stats)
         images, sec, n, b, stamps = _timed_batches(torch, it, ctx["steps"], min_seconds, ctx["sampler"], ctx["barrier"])
+        stats = {k: dl.stats[k] - before[k] for k in ("consumer_wait_s", "producer_wait_s")}   # of the timed window
         check = check_batch(np, S, next(it), config, h, w, flipped_depth=depth_flip)
         per_item = h * w * 4 * (2 if depth_flip else 1)
         h2d = _annotation_bytes(torch, b, batch) + batch * per_item
-        stats = dict(dl.stats)
         win = max(1, min(20, len(stamps) // 5))
         rates = sorted(win * batch / (stamps[i + win] - stamps[i]) for i in range(0, len(stamps) - win, win)
                        if stamps[i + win] > stamps[i])
@@ -595,11 +596,13 @@ def replay_leg(ctx, cfg, prefix, cache=None, min_seconds=2.0, project=None, dept
         for _ in range(ctx["warmup"] + 3 + producers):
             next(it)["image_stats"].cpu()
         torch.cuda.synchronize(ctx["dev"])
+        waited = dl.stats["consumer_wait_s"]
         images, sec, n, b, _ = _timed_batches(torch, it, ctx["steps"], min_seconds, ctx["sampler"], ctx["barrier"])
+        waited = dl.stats["consumer_wait_s"] - waited
         check = check_batch(np, S, next(it), config, h, w, flipped_depth=depth_flip, pool=cfg.get("pool", 16))
         per_item = h * w * 4 * (2 if depth_flip else 1)
         return {"images": images, "sec": sec, "batches": n, "check": check, "bytes_per_image": per_item,
-                "cache_fill_s": dl.stats.get("cache_fill_s"), "consumer_wait_s": dl.stats["consumer_wait_s"]}
+                "cache_fill_s": dl.stats.get("cache_fill_s"), "consumer_wait_s": waited}
     finally:
         if it is not None:
             it.close()
