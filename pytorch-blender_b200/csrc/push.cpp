@@ -174,8 +174,12 @@ void accept_pending(Endpoint& e) {
   while (e.listen_fd >= 0) {
     int fd = accept4(e.listen_fd, nullptr, nullptr, SOCK_NONBLOCK | SOCK_CLOEXEC);
     if (fd < 0) return;
-    int big = 4 << 20, one = 1;
-    setsockopt(fd, SOL_SOCKET, SO_SNDBUF, &big, sizeof big);
+    int one = 1;
+    static const int sndbuf = [] {
+      const char* e = getenv("BT_PUSH_SNDBUF");   // bytes; tuning knob
+      return e ? atoi(e) : (1 << 20);
+    }();
+    if (sndbuf > 0) setsockopt(fd, SOL_SOCKET, SO_SNDBUF, &sndbuf, sizeof sndbuf);
     setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);   // fails harmlessly on AF_UNIX
     if (handshake(fd) != BT_OK) { close(fd); continue; }
     PushPeer* slot = nullptr;

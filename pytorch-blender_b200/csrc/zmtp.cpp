@@ -295,8 +295,11 @@ namespace {
 void start_connect(Peer& p) {
   p.fd = socket(p.family, SOCK_STREAM | SOCK_NONBLOCK | SOCK_CLOEXEC, 0);
   if (p.fd < 0) { p.retry_at = now_ms() + 200; return; }
-  int big = 4 << 20;
-  setsockopt(p.fd, SOL_SOCKET, SO_RCVBUF, &big, sizeof big);
+  static const int rcvbuf = [] {
+    const char* e = getenv("BT_PULL_RCVBUF");   // bytes; tuning knob
+    return e ? atoi(e) : (1 << 20);
+  }();
+  if (rcvbuf > 0) setsockopt(p.fd, SOL_SOCKET, SO_RCVBUF, &rcvbuf, sizeof rcvbuf);
   int rc = connect(p.fd, reinterpret_cast<sockaddr*>(&p.addr), p.addrlen);
   if (rc == 0 || errno == EINPROGRESS) {
     p.state = Peer::CONNECTING;

@@ -1,42 +1,82 @@
 #!/usr/bin/env python3
-"""Sweep receiver threads / ZMQ I/O threads / transport for the end-to-end leg (diagnostic)."""
+"""End-to-end rate of the headline stream leg for chosen core sets and thread splits (diagnostic):
+    python tools/e2e_sweep.py --cpus 0-7 --split 2x4 3x4 --transport tcp ipc [--python-publishers]
+Prints one JSON line per case."""
+import argparse
 import json
+import os
 import sys
+import time
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent
 sys.path[:0] = [str(ROOT), str(ROOT / "pytorch-blender_b200")]
-import torch  # noqa: E402
-
 import bench  # noqa: E402
-from blendtorch import btt  # noqa: E402
 
 
-class _S:
-    active = False
+def parse_cpus(text):
+    out = []
+    for part in text.split(","):
+        a, _, b = part.partition("-")
+        out += list(range(int(a), int(b or a) + 1))
+    return out
 
 
 def main():
-    dev = torch.device("cuda", 0)
-    torch.cuda.set_device(0)
-    res = []
-    combos = [("tcp", 4, 1), ("tcp", 8, 1), ("tcp", 2, 5), ("tcp", 3, 5), ("tcp", 4, 3), ("ipc", 4, 1), ("ipc", 8, 1),
-              ("ipc", 2, 5), ("ipc", 3, 5), ("ipc", 6, 2)]
-    if len(sys.argv) > 1:
-        combos = [tuple(int(x) if x.isdigit() else x for x in a.split(",")) for a in sys.argv[1:]]
-    for combo in combos:
-        transport, recv, io = combo[:3]
-        shm_slots = combo[3] if len(combo) > 3 else 0
-        bench.PUBLISHERS = combo[4] if len(combo) > 4 else 5
-        rxmode = combo[5] if len(combo) > 5 else "auto"
-        raw = len(combo) > 6 and combo[6] == "raw"
-        images, sec, h2d, d2h = bench.e2e_leg(torch, btt, dev, 600, 10, _S(), transport, recv, io, shm_slots, rxmode,
-                                              raw_parts=raw)
-        r = {"transport": transport, "rx": rxmode, "receivers": recv, "io_threads": io, "shm_slots": shm_slots,
-             "publishers": bench.PUBLISHERS, "raw_parts": raw, "images_per_s": images / sec,
-             "GBps": images / sec * 1228800 / 1e9}
-        print(json.dumps(r), flush=True)
-        res.append(r)
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cpus", default="")
+    ap.add_argument("--split", nargs="+", default=["5x8"], help="SENDERSxRECEIVERS")
+    ap.add_argument("--transport", nargs="+", default=["tcp"])
+    ap.add_argument("--seconds", type=float, default=1.5)
+    ap.add_argument("--shm-slots", type=int, default=0)
+    ap.add_argument("--python-publishers", action="store_true")
+    ap.add_argument("--gpu", type=int, default=0)
+    ap.add_argument("--tag", default="")
+    a = ap.parse_args()
+    cpus = parse_cpus(a.cpus) if a.cpus else sorted(os.sched_getaffinity(0))
+    os.sched_setaffinity(0, cpus)
+    import numpy as np
+    import torch
+    from blendtorch import btt
+    from blendtorch.btt import native as N, synthetic as S
+    torch.set_num_threads(1)
+    dev = torch.device("cuda", a.gpu)
+    torch.cuda.set_device(a.gpu)
+    ctx = {"torch": torch, "btt": btt, "np": np, "S": S, "N": N, "dev": dev, "rank": a.gpu, "local": a.gpu, "world": 1,
+           "cpus": cpus, "steps": 20, "warmup": 5, "sampler": None, "barrier": lambda: torch.cuda.synchronize(dev)}
+    c2 = {"name": "C2", "config": 2, "h": bench.H, "w": bench.W, "batch": bench.BATCH, "publishers": bench.PUBLISHERS}
+    for tr in a.transport:
+        for sp in a.split:
+            s, r = (int(x) for x in sp.split("x"))
+            if a.python_publishers:
+                orig = bench.spawn_native_publisher
+
+                def py(n, transport="tcp", threads=1, tag="n", extra=(), cpus=None, config=None, h=None, w=None):
+                    addrs, procs = bench.spawn_publishers("blendtorch.btt.synthetic", n, transport, tag=tag, extra=extra)
+                    for p in procs:
+                        os.sched_setaffinity(p.pid, cpus)
+
+                    class Group:
+                        pid = procs[0].pid
+
+                        def send_signal(self, sig):
+                            [p.send_signal(sig) for p in procs]
+
+                        def wait(self, timeout=None):
+                            [p.wait(timeout) for p in procs]
+
+                        def kill(self):
+                            [p.kill() for p in procs]
+                    return addrs, Group()
+                bench.spawn_native_publisher = py
+            t0 = time.time()
+            leg = bench.stream_leg(ctx, c2, tr, r, s, shm_slots=a.shm_slots, min_seconds=a.seconds)
+            if a.python_publishers:
+                bench.spawn_native_publisher = orig
+            print(json.dumps({"tag": a.tag, "gpu": a.gpu, "cpus": len(cpus), "transport": tr, "senders": s if not a.python_publishers else "5 python procs",
+                              "receivers": r, "shm_slots": a.shm_slots,
+                              "images_per_s": leg["images"] / leg["sec"], "GBps": leg["images"] / leg["sec"] * 1228800 / 1e9,
+                              "consumer_wait_s": leg["consumer_wait_s"], "check": leg["check"], "leg_s": time.time() - t0}), flush=True)
 
 
 if __name__ == "__main__":
