@@ -530,11 +530,14 @@ def _annotation_bytes(torch, b, batch):
                if isinstance(v, torch.Tensor) and k in ("btid", "frameid", "bbox", "xy", "corners"))
 
 
-def stream_leg(ctx, cfg, transport, receivers, senders, shm_slots=0, min_seconds=2.0, project=None, depth_flip=False):
+def stream_leg(ctx, cfg, transport, receivers, senders, shm_slots=0, min_seconds=2.0, project=None, depth_flip=False,
+               in_place=False):
     """Public API with host buffers: native publishers -> DeviceLoader -> device batch (+ stats read back)."""
     torch, btt, np, S = ctx["torch"], ctx["btt"], ctx["np"], ctx["S"]
     h, w, batch, npub, config = cfg["h"], cfg["w"], cfg["batch"], cfg["publishers"], cfg["config"]
     extra = ("--shm-slots", str(shm_slots)) if shm_slots else ()
+    if in_place:
+        extra += ("--in-place",)
     senders = max(1, min(senders, npub))
     addrs, proc = spawn_native_publisher(npub, transport, threads=senders, tag="r%d%s" % (ctx["rank"], cfg["name"]),
                                          extra=extra, cpus=ctx["cpus"], config=config, h=h, w=w)
@@ -787,6 +790,8 @@ def ours(args):
     shm_senders = max(1, min(PUBLISHERS, len(cpus) - 2))
     legs["shm"] = stream_leg(ctx, c2, args.transport, min(2, receivers), shm_senders, shm_slots=args.shm_slots)
     barrier()
+    legs["shm_in_place"] = stream_leg(ctx, c2, args.transport, min(2, receivers), 1, shm_slots=args.shm_slots, in_place=True)
+    barrier()
 
     # ---- the other BASELINE.json shapes ---------------------------------------------------------------
     tmp = tempfile.mkdtemp(prefix="btrec_r%d_" % rank, dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
@@ -845,7 +850,9 @@ def _report(args, ctx, gather, dist, dleg, value, achieved, sec_per_launch, algo
     world, rank, cpus = ctx["world"], ctx["rank"], ctx["cpus"]
     h2d_conc = gather(probes["pcie_h2d_gbs"])
     memcpy_conc = gather(probes["host_memcpy_gbs"])
-    pcie = min(h2d_conc)          # per GPU, with every GPU copying at once: the figure fractions are quoted against
+    pcie = sum(h2d_conc) / world   # mean per GPU with every GPU copying at once: what fractions are quoted against
+    nbytes = H * W * C
+    memcpy_total = sum(memcpy_conc)
 
     def leg_json(leg, note=None):
         rate = sum(gather(leg["images"])) / max(gather(leg["sec"]))     # whole job: all images / the slowest rank's window
@@ -869,6 +876,7 @@ def _report(args, ctx, gather, dist, dleg, value, achieved, sec_per_launch, algo
         if kt:
             configs[name]["kernels"] = kt
     e2e, ipc, shm = leg_json(legs["tcp"]), leg_json(legs["ipc"]), leg_json(legs["shm"])
+    shm_ip = leg_json(legs["shm_in_place"])
     tcp = legs["tcp"]
 
     cpu = None
@@ -887,7 +895,7 @@ def _report(args, ctx, gather, dist, dleg, value, achieved, sec_per_launch, algo
         single = algo_bytes / dleg["single"]["sec_per_launch"] / 1e9
         e2ek = algo_bytes / dleg["e2e_kernel"]["sec_per_launch"] / 1e9
         k4 = configs.get("C4", {}).get("kernels", {}).get("k1_gbs")
-        checks = [e2e, ipc, shm] + list(configs.values())
+        checks = [e2e, ipc, shm, shm_ip] + list(configs.values())
         line = {
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec_per_launch * 1e3, "higher_is_better": True,
@@ -929,6 +937,9 @@ def _report(args, ctx, gather, dist, dleg, value, achieved, sec_per_launch, algo
             "e2e_shm_wire": dict(shm, note="opt-in wire for co-located producers: payload goes producer -> shared "
                                  "memory -> DMA, no consumer-side CPU copy; not the reference's pickle wire, reported beside "
                                  "e2e, not instead of it (%d slots per publisher)" % args.shm_slots),
+            "e2e_shm_wire_in_place": dict(shm_ip, note="same wire, frames published from where they stand in shared memory "
+                                          "(a producer that renders into the segment: no producer-side copy either); "
+                                          "every payload byte crosses host memory once, as a DMA read"),
             "e2e_replay": configs.get("C1"),
             "e2e_replay_cache_host": configs.get("C1_cache_host"),
             "configs": configs,
@@ -938,6 +949,17 @@ def _report(args, ctx, gather, dist, dleg, value, achieved, sec_per_launch, algo
                      "socket_path_images_per_s": probes["socket_path_images_per_s"],
                      "socket_path_note": "native publishers -> direct receivers into an unpinned ring, same thread split, "
                                          "every rank at once, no GPU: the ceiling of the pickle wire on these cores",
+                     "memory_ceilings": {
+                         "host_memcpy_gbs_total": memcpy_total,
+                         "pickle_wire_images_per_s": memcpy_total / 2.5 * 1e9 / nbytes,
+                         "one_copy_images_per_s": memcpy_total / 1.5 * 1e9 / nbytes,
+                         "dma_only_images_per_s": sum(h2d_conc) * 1e9 / nbytes,
+                         "note": "host memory bandwidth is shared by all ranks.  In units of the concurrent memcpy rate "
+                                 "(1 copy = 1 read + 1 write), a payload byte costs 2 copies + 1 DMA read = 2.5 on the socket "
+                                 "wire (sender -> kernel, kernel -> pinned, DMA), 1.5 with one CPU copy (shared-memory wire "
+                                 "with a copying producer; replay from the page cache), and only the DMA read when frames "
+                                 "already stand in page-locked memory (in-place shared memory, cache='host'): those scale "
+                                 "with the GPUs' concurrent PCIe rate instead"},
                      "sender_images_per_s_per_thread": s_rate, "receiver_images_per_s_per_thread": r_rate,
                      "thread_split": "senders %d, receivers %d per rank (from the per-thread rates)" % (senders, receivers)},
             "gpu_launches": dleg["overlapped"]["launches_timed"],

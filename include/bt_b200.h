@@ -325,6 +325,9 @@ int bt_push_send(bt_push* p, int endpoint, const uint8_t* const* parts, const ui
  * payload[m] (payload_len[m] bytes) is copied into a free slot and tmpl[m] -- the pickled message with
  * the array replaced by ("__btshm__", name, ticket, dtype, shape), whose ticket is a 4-byte BININT at
  * byte tmpl_ticket_off[m] -- is sent with that slot's ticket patched in.
+ * With seg non-null and payload NULL frames are published *in place*, the way a renderer that draws
+ * straight into shared memory does: slot k already holds the frame that tmpl[k] describes (pool_n must
+ * equal the slot count), publishing is acquiring a free slot and sending its template -- no producer copy.
  * *sent (optional) is updated as messages go out.  Returns BT_OK when all were sent or stop was seen. */
 typedef struct bt_push_job {
   int first_endpoint, n_endpoints, pool_n, reserved;

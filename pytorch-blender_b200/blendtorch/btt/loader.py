@@ -138,12 +138,18 @@ class _Stager:
     def ingest(self, slot, item, msg, host_rows):
         self.ring.ingest(slot, self.schema, item, msg, host_rows)
 
-    def finish(self, slot, n, host_rows, cache=None, idx=None, fill=None):
+    def finish(self, slot, n, host_rows, cache=None, idx=None, fill=None, batch_size=None):
+        """Enqueue, on this stager's stream, everything that turns the `n` staged items into device
+        batches: the column copies, the kernels, an event.  The items are handed out as batches of
+        `batch_size` (default: one batch) that share one set of allocations, one copy per column and
+        -- unless per-batch statistics are wanted -- one launch per kernel: the per-batch cost of the
+        host side is a handful of slices.  Returns (list of batch dicts, event, tensors to keep, idx)."""
         sch = self.schema
+        B = n if not batch_size else batch_size
         used = 0
         for _, off, ib, _, _, _ in self.plan:
             used = max(used, off + n * ib)
-        batch = {}
+        batch, per_batch = {}, {}
         raw = torch.empty(max(used, 1), dtype=torch.uint8, device=self.device)
         if used and fill is not None:
             fill(raw, self._stream_handle)      # e.g. rows gathered from a pinned recording
@@ -158,11 +164,11 @@ class _Stager:
             if prep is None or self.keep_raw:
                 t = raw[off:off + n * ib].view(dt).view((n,) + shape)
             if prep is not None:
-                out, stats = prep.run(base + off, n, self._stream_handle)
+                out, stats = prep.run_group(base + off, n, B, self._stream_handle)
                 self.kernels += prep.last_kernels
                 keep.append(out)
                 if stats is not None:
-                    batch[key + "_stats"] = stats
+                    per_batch[key + "_stats"] = stats
                     keep.append(stats)
                 if self.keep_raw:
                     batch[key + "_raw"] = t
@@ -175,7 +181,19 @@ class _Stager:
         ev.record(self.stream)
         for k in sch.host_keys:
             batch[k] = host_rows.get(k, [])
-        return batch, ev, keep, (idx if cache is not None else None)
+        # what the resident cache needs once the consumer has seen the group: rows and host-side fields
+        tag = (idx, {k: batch[k] for k in sch.host_keys}) if cache is not None else None
+        if n <= B:
+            for k, v in per_batch.items():
+                batch[k] = v[0]
+            return [batch], ev, keep, tag
+        parts = []
+        for j, first in enumerate(range(0, n, B)):
+            d = {k: v[first:first + B] for k, v in batch.items()}
+            for k, v in per_batch.items():
+                d[k] = v[j]
+            parts.append(d)
+        return parts, ev, keep, tag
 
     def close(self):
         self.stream.synchronize()
@@ -281,6 +299,11 @@ class DeviceLoader:
         (dataset.py:103,105), and unpickling data from a socket can run code; the native scanner only
         locates payloads.  With False, a message outside its subset raises instead of being decoded by
         ``pickle.loads`` (so no item_transform, no recording tee, no string fields).
+    group: how many batches are staged, copied and preprocessed together (one pinned slot, one
+        allocation, one copy per column and one launch per kernel for `group` batches, which are then
+        handed out one by one as slices): the host cost per batch of small batches all but disappears
+        and the copies and launches get longer.  None = as many as make about 32 MiB, at most 8; 1 =
+        every batch by itself.  Batches of a group share their storage; results are the same.
     cache: 'device' keeps a replayed recording resident in HBM (raw columns, i.e. uint8 frames): the
         first epoch fills it on the way through, every later epoch is served from it -- no file, host
         or PCIe traffic; K1 gathers the sampler's frames straight from the resident set.  Only for
@@ -296,7 +319,7 @@ class DeviceLoader:
     def __init__(self, dataset, batch_size=1, shuffle=False, drop_last=False, device="cuda",
                  preprocess=None, num_receivers=None, ring_depth=3, prefetch=2, ingest_threads=4,
                  seed=0, keep_raw=False, io_threads=1, project=None, transport="auto", cache=None,
-                 cache_bytes=None, allow_pickle=True):
+                 cache_bytes=None, allow_pickle=True, group=None):
         self.dataset = dataset
         self.batch_size = int(batch_size)
         if self.batch_size < 1:
@@ -323,6 +346,9 @@ class DeviceLoader:
         self.ring_depth, self.prefetch = int(ring_depth), int(prefetch)
         self.ingest_threads = int(ingest_threads)
         self.seed, self.keep_raw = seed, keep_raw
+        if group is not None and int(group) < 1:
+            raise ValueError("group must be >= 1")
+        self.group = None if group is None else int(group)
         self.io_threads = max(1, int(io_threads))
         if transport not in ("auto", "direct", "zmq"):
             raise ValueError("transport must be 'auto', 'direct' or 'zmq'")
@@ -363,17 +389,36 @@ class DeviceLoader:
         return n // self.batch_size if self.drop_last else -(-n // self.batch_size)
 
     # ---- producers --------------------------------------------------------------------------
-    def _new_stager(self, first_msg, rid=0, sizes=None, depth=None):
+    _GROUP_BYTES = 32 << 20
+
+    def _group_for(self, item_bytes):
+        """Batches per group for items of `item_bytes`."""
+        if self.group is not None:
+            return self.group
+        per_batch = max(1, item_bytes * self.batch_size)
+        return int(max(1, min(8, -(-self._GROUP_BYTES // per_batch))))
+
+    def _group_of_message(self, first_msg, sizes=None):
+        try:
+            probe = Schema.from_message(first_msg, 1, sizes, self.allow_pickle)
+        except Exception:
+            return 1
+        try:
+            return self._group_for(sum(c.item_bytes for c in probe.columns))
+        finally:
+            probe.close()
+
+    def _new_stager(self, first_msg, rid=0, sizes=None, depth=None, group=1):
         """Stager for the stream that starts with `first_msg`.  Pinned rings are expensive to create
         (page-locking hundreds of MB takes longer than an epoch of small recordings), so a stager
         is kept per producer and reused by later epochs while the layout stays the same."""
-        schema = Schema.from_message(first_msg, self.batch_size, sizes, self.allow_pickle)
+        schema = Schema.from_message(first_msg, self.batch_size * group, sizes, self.allow_pickle)
         for key, spec in self.specs.items():
             c = schema.column(key)  # KeyError: the named image field is not in the messages
             if c.dtype != np.uint8 and not isinstance(spec, FlipRows):
                 raise TypeError("field %r is %s; Preprocess takes uint8 frames (FlipRows flips anything)" % (key, c.dtype))
         depth = self.ring_depth if depth is None else depth
-        sig = (schema.native, tuple((c.key, c.kind, c.dtype.str, c.shape, c.slot_off) for c in schema.columns),
+        sig = (schema.batch, schema.native, tuple((c.key, c.kind, c.dtype.str, c.shape, c.slot_off) for c in schema.columns),
                schema.host_keys, depth)
         cached = self._stagers.get(rid)
         if cached is not None and cached[0] == sig:
@@ -470,7 +515,7 @@ class DeviceLoader:
         self.stats["cache_fill_s"] = time.perf_counter() - t0
 
     def _emit(self, out_q, stop, stager, slot, n, host_rows, cache=None, idx=None, fill=None):
-        item = stager.finish(slot, n, host_rows, cache, idx, fill)
+        item = stager.finish(slot, n, host_rows, cache, idx, fill, self.batch_size)
         self.stats["bytes_h2d"] += stager.item_bytes * n
         t0 = time.perf_counter()
         try:
@@ -559,12 +604,13 @@ class DeviceLoader:
                 assert waited < ds.timeoutms, "No response within timeout interval."
             if remaining <= 0:
                 return
-            stager = self._new_stager(rx.pending(), self._rid(), rx.pending_parts())
+            group = self._group_of_message(rx.pending(), rx.pending_parts())
+            stager = self._new_stager(rx.pending(), self._rid(), rx.pending_parts(), group=group)
             holder.append(stager)
             ring, schema = stager.ring, stager.schema
             while remaining > 0 and not stop.is_set():
                 slot, filled, host_rows = stager.begin(), 0, {}
-                want = min(self.batch_size, remaining)
+                want = min(self.batch_size * group, remaining)
                 waited = 0
                 while filled < want:
                     if schema.native:
@@ -580,6 +626,8 @@ class DeviceLoader:
                         waited += 100
                         if stop.is_set():
                             return
+                        if filled and filled % self.batch_size == 0:
+                            break    # the stream paused on a batch boundary: hand out what is complete
                         # the stream stalled: do not sit on shared-memory slots of a partly filled
                         # batch (their publishers may be waiting for exactly those slots)
                         ring.spill(slot, schema)
@@ -593,8 +641,11 @@ class DeviceLoader:
                     filled += 1
                     waited = 0
                 remaining -= filled
-                if filled < self.batch_size and self.drop_last:
-                    break
+                if self.drop_last and filled % self.batch_size:      # only the very last batch can be short
+                    filled -= filled % self.batch_size
+                    remaining = 0
+                    if not filled:
+                        break
                 if not self._emit(out_q, stop, stager, slot, filled, host_rows):
                     return
         finally:
@@ -679,16 +730,20 @@ class DeviceLoader:
             custom = ds.has_custom_item()
             B = self.batch_size
             n_prod = self._replay_producers()
-            for start in range(rid * B, len(order), B * n_prod):   # producer `rid` takes batches rid, rid+n, ...
+            group = 1 if custom or not len(order) else self._group_of_message(readers[0].raw(0))
+            G = B * group
+            for start in range(rid * G, len(order), G * n_prod):   # producer `rid` takes groups rid, rid+n, ...
                 if stop.is_set():
                     return
-                idx = order[start:start + B]
-                if len(idx) < B and self.drop_last:
-                    break
+                idx = order[start:start + G]
+                if self.drop_last and len(idx) % B:
+                    idx = idx[:len(idx) // B * B]
+                    if not len(idx):
+                        break
                 if self._host is not None:
                     # the recording is in page-locked memory: this batch is a handful of DMA copies
                     if stager is None:
-                        stager = self._new_stager(readers[0].raw(0), rid, depth=0)
+                        stager = self._new_stager(readers[0].raw(0), rid, depth=0, group=group)
                         order_dev = torch.from_numpy(np.ascontiguousarray(order, dtype=np.int64)).to(self.device)
                     host, plan = self._host, stager.plan
                     if not self._emit(out_q, stop, stager, None, len(idx), {}, None, None,
@@ -713,7 +768,7 @@ class DeviceLoader:
                         m = fidx == f
                         addrs[m], lens[m] = readers[f].spans(local[m])
                     if stager is None:
-                        stager = self._new_stager(readers[fidx[0]].raw(int(local[0])), rid)
+                        stager = self._new_stager(readers[fidx[0]].raw(int(local[0])), rid, group=group)
                     slot, host_rows = stager.begin(), {}
                     done = 0
                     if stager.schema.native:
@@ -844,16 +899,17 @@ class DeviceLoader:
                     continue
                 if isinstance(item, BaseException):
                     raise item
-                batch, ev, keep, idx = item
+                batches, ev, keep, tag = item
                 cur = torch.cuda.current_stream(self.device)
                 cur.wait_event(ev)
                 for t in keep:
                     t.record_stream(cur)
-                if idx is not None and self._cache is not None:
-                    self._cache.commit(idx, batch)
-                self.stats["batches"] += 1
-                self.stats["items"] += len(batch["btid"]) if "btid" in batch else next((len(v) for v in batch.values()), 0)
-                yield batch
+                if tag is not None and self._cache is not None:
+                    self._cache.commit(tag[0], tag[1])
+                for batch in batches:          # the batches of one group, in order
+                    self.stats["batches"] += 1
+                    self.stats["items"] += len(batch["btid"]) if "btid" in batch else next((len(v) for v in batch.values()), 0)
+                    yield batch
                 if ordered:
                     turn = (turn + 1) % n_prod
         finally:

@@ -217,6 +217,38 @@ class PreparedPreprocess:
         return out, stats
 
 
+    def run_group(self, src_ptr, n, batch, stream_handle):
+        """`n` dense frames that will be handed out as batches of `batch`: one output allocation for all
+        of them and, without statistics, one launch; with statistics one launch per batch (they are
+        per-batch results), writing into slices of the same output.  Returns (out, stats) with stats of
+        shape (number of batches, C_out, 2) or None."""
+        out = torch.empty(self.out_shape(n), dtype=self.spec.dtype, device=self.device)
+        self.last_kernels = 0
+        p = self.params
+        p.src_index = None
+        if not self.spec.stats:
+            if n:
+                p.src, p.dst, p.batch = src_ptr, out.data_ptr(), n
+                N.check(N.lib.bt_preprocess_launch(self._ref, stream_handle))
+                self.last_kernels = 1
+            return out, None
+        nb = max(1, -(-n // batch))
+        stats = torch.empty((nb, self.cout, 2), dtype=torch.float64, device=self.device)
+        if n == 0:
+            return out, stats.zero_()
+        in_item = self.h * self.w * self.c
+        out_item = self.h * self.w * self.cout * out.element_size()
+        dst, st = out.data_ptr(), stats.data_ptr()
+        for b in range(nb):
+            first = b * batch
+            p.src, p.dst = src_ptr + first * in_item, dst + first * out_item
+            p.batch = min(batch, n - first)
+            p.stats_out = st + b * self.cout * 16
+            N.check(N.lib.bt_preprocess_launch(self._ref, stream_handle))
+            self.last_kernels += N.lib.bt_preprocess_last_kernels()
+        return out, stats
+
+
 @dataclass
 class FlipRows:
     """Vertical flip of a field K1 does not take -- a float32 depth map, a uint16 mask -- sent bottom-up.
@@ -260,6 +292,9 @@ class PreparedFlip:
         for d in shape[1:]:
             self.row_bytes *= d
         self.last_kernels = 0
+
+    def run_group(self, src_ptr, n, batch, stream_handle):
+        return self.run(src_ptr, n, stream_handle)
 
     def run(self, src_ptr, n, stream_handle, index_ptr=None):
         out = torch.empty((n,) + self.shape, dtype=self.dtype, device=self.device)

@@ -157,7 +157,9 @@ class NativePublisher:
 
         shm: None for the reference wire, or ``(segments, payloads, ticket_offsets)`` for the
         shared-memory wire (shm.py): per endpoint a `shm.Segment`, per message the array that travels
-        through it and the byte offset of the 4-byte ticket inside the pickled template."""
+        through it and the byte offset of the 4-byte ticket inside the pickled template.  `payloads`
+        None publishes in place: slot k of the segment already holds the array template k describes
+        (one template per slot), as when a renderer draws straight into shared memory."""
         import threading
         C, N = self._C, self._N
         n_ep = len(self.addresses)
@@ -181,15 +183,16 @@ class NativePublisher:
             if shm is not None:
                 segs, payloads, offs = shm
                 sh = (C.c_void_p * count)(*[s.handle for s in segs[first:first + count]])
-                pp, pl, po = (C.c_void_p * n)(), (C.c_uint64 * n)(), (C.c_uint32 * n)()
-                fp = [a for row in payloads[first:first + count] for a in row]
-                fo = [o for row in offs[first:first + count] for o in row]
-                for i, (a, o) in enumerate(zip(fp, fo)):
-                    pp[i], pl[i] = N.buffer_address(a)
-                    po[i] = o
-                job.seg, job.payload = C.cast(sh, C.c_void_p), C.cast(pp, C.c_void_p)
-                job.payload_len, job.tmpl_ticket_off = C.cast(pl, C.c_void_p), C.cast(po, C.c_void_p)
-                keep += [sh, pp, pl, po, fp, segs]
+                po = (C.c_uint32 * n)(*[o for row in offs[first:first + count] for o in row])
+                job.seg, job.tmpl_ticket_off = C.cast(sh, C.c_void_p), C.cast(po, C.c_void_p)
+                keep += [sh, po, segs]
+                if payloads is not None:     # None: frames already stand in their slots (published in place)
+                    pp, pl = (C.c_void_p * n)(), (C.c_uint64 * n)()
+                    fp = [a for row in payloads[first:first + count] for a in row]
+                    for i, a in enumerate(fp):
+                        pp[i], pl[i] = N.buffer_address(a)
+                    job.payload, job.payload_len = C.cast(pp, C.c_void_p), C.cast(pl, C.c_void_p)
+                    keep += [pp, pl, fp]
             sent = C.c_int64(0)
             job.stop = C.cast(C.pointer(self._stop), C.c_void_p)
             job.sent = C.cast(C.pointer(sent), C.c_void_p)

@@ -164,10 +164,13 @@ def shm_templates(objs, segment, protocol=3):
 
 
 def run_native_publishers(binds, btids, config, h, w, c=4, count=-1, pool=16, protocol=3, threads=1,
-                          shm_slots=0, ready=None, stop=None):
+                          shm_slots=0, ready=None, stop=None, in_place=False):
     """All publishers of one consumer in this process: one `NativePublisher` endpoint per bind address,
     cycling the same deterministic pools as `run_publisher`, on `threads` sender threads.  Blocks until
-    every endpoint has sent `count` messages, or (count < 0) until `stop` (a threading.Event) is set."""
+    every endpoint has sent `count` messages, or (count < 0) until `stop` (a threading.Event) is set.
+    in_place (with shm_slots): the frames are written into the segment's slots once, before the first
+    message, and published from where they stand -- a producer that renders straight into shared
+    memory, so that no producer-side copy is part of what a consumer benchmark measures."""
     from .publisher import NativePublisher
     pub = NativePublisher(list(binds))
     segs = []
@@ -178,14 +181,20 @@ def run_native_publishers(binds, btids, config, h, w, c=4, count=-1, pool=16, pr
             for btid in btids:
                 rng = rng_for(config, btid)
                 objs = [message(rng, config, btid, i, h, w, c) for i in range(pool)]
+                if in_place:   # slot k holds frame k % pool for good; one template per slot
+                    objs = [objs[k % pool] for k in range(shm_slots)]
                 big = max(v.nbytes for v in objs[0].values() if isinstance(v, np.ndarray))
                 seg = shm.Segment(big, shm_slots)
+                seg.set_lease(0)
                 segs.append(seg)
                 t, p, o = shm_templates(objs, seg, protocol=protocol)
+                if in_place:
+                    for k, a in enumerate(p):
+                        seg.view(k)[:a.nbytes] = a.reshape(-1).view(np.uint8)
                 pools.append(t)
                 payloads.append(p)
                 offs.append(o)
-            pub.start(pools, messages=count, threads=threads, shm=(segs, payloads, offs))
+            pub.start(pools, messages=count, threads=threads, shm=(segs, None if in_place else payloads, offs))
         else:
             pools = [pickled_pool(config, btid, h, w, c, pool, protocol) for btid in btids]
             pub.start(pools, messages=count, threads=threads)
@@ -222,6 +231,7 @@ def main(argv=None):
     ap.add_argument("--send-hwm", type=int, default=10)
     ap.add_argument("--shm-slots", type=int, default=0)
     ap.add_argument("--raw-parts", action="store_true")
+    ap.add_argument("--in-place", action="store_true", help="--native --shm-slots: publish frames from where they stand")
     a = ap.parse_args(argv)
     h, w, c = CONFIG_SHAPES.get(a.config, (480, 640, 4))
     h, w, c = a.height or h, a.width or w, a.channels or c
@@ -232,7 +242,8 @@ def main(argv=None):
         os.sched_setaffinity(0, {int(x) for x in a.cpus.split(",")})
     if a.native:
         btids = list(range(a.btid, a.btid + len(a.bind)))
-        run_native_publishers(a.bind, btids, a.config, h, w, c, a.count, a.pool, a.protocol, a.threads, a.shm_slots)
+        run_native_publishers(a.bind, btids, a.config, h, w, c, a.count, a.pool, a.protocol, a.threads, a.shm_slots,
+                              in_place=a.in_place)
         return 0
     if len(a.bind) != 1:
         ap.error("several --bind addresses need --native")

@@ -446,8 +446,15 @@ int bt_push_run(bt_push* p, const bt_push_job* job) {
   if (!p || !job || job->first_endpoint < 0 || job->n_endpoints < 1 ||
       job->first_endpoint + job->n_endpoints > (int)p->eps.size() || job->pool_n < 1 || !job->pool || !job->pool_len)
     return bt::fail(BT_E_INVALID, "bt_push_run: bad arguments");
-  if (job->seg && (!job->payload || !job->payload_len || !job->tmpl_ticket_off))
-    return bt::fail(BT_E_INVALID, "bt_push_run: the shared-memory wire needs payloads and ticket offsets");
+  if (job->seg && !job->tmpl_ticket_off)
+    return bt::fail(BT_E_INVALID, "bt_push_run: the shared-memory wire needs ticket offsets");
+  if (job->seg && (job->payload == nullptr) != (job->payload_len == nullptr))
+    return bt::fail(BT_E_INVALID, "bt_push_run: payload and payload_len go together");
+  const bool in_place = job->seg && !job->payload;   // frames are produced inside the slots (see bt_b200.h)
+  if (in_place)
+    for (int i = 0; i < job->n_endpoints; ++i)
+      if (bt_shm_nslots(job->seg[i]) != job->pool_n)
+        return bt::fail(BT_E_INVALID, "bt_push_run: in-place publishing needs one template per slot (pool_n == slots)");
   const int first = job->first_endpoint, count = job->n_endpoints;
   for (int i = first; i < first + count; ++i) p->eps[i]->started = 0;
   std::vector<pollfd> pfds;
@@ -470,17 +477,22 @@ int bt_push_run(bt_push* p, const bt_push_job* job) {
           if (q.fd < 0) continue;
           if (q.nframes == 0) {
             if (!(job->messages < 0 || e.started < job->messages)) continue;
-            const size_t m = (size_t)ei * job->pool_n + (size_t)(e.started % job->pool_n);
+            size_t m = (size_t)ei * job->pool_n + (size_t)(e.started % job->pool_n);
             if (job->seg) {
               bt_shm* seg = job->seg[ei];
               int ticket = -1;
               if (bt_shm_acquire(seg, 0, &ticket) != BT_OK) { busy = true; continue; }   // consumers hold every slot
-              if (job->payload_len[m] > bt_shm_slot_bytes(seg)) {
-                bt_shm_release(seg, ticket);
-                return bt::fail(BT_E_TOO_LARGE, "payload of %llu bytes does not fit a shared-memory slot",
-                                (unsigned long long)job->payload_len[m]);
+              if (in_place) {
+                // the producer wrote this frame where it stands: slot k holds the frame template k describes
+                m = (size_t)ei * job->pool_n + (size_t)(ticket & 0xFFFF);
+              } else {
+                if (job->payload_len[m] > bt_shm_slot_bytes(seg)) {
+                  bt_shm_release(seg, ticket);
+                  return bt::fail(BT_E_TOO_LARGE, "payload of %llu bytes does not fit a shared-memory slot",
+                                  (unsigned long long)job->payload_len[m]);
+                }
+                memcpy(bt_shm_slot_ptr(seg, ticket), job->payload[m], job->payload_len[m]);
               }
-              memcpy(bt_shm_slot_ptr(seg, ticket), job->payload[m], job->payload_len[m]);
               q.small.assign(job->pool[m], job->pool[m] + job->pool_len[m]);
               if ((uint64_t)job->tmpl_ticket_off[m] + 4 > q.small.size()) {
                 bt_shm_release(seg, ticket);

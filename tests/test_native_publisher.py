@@ -160,14 +160,16 @@ def test_direct_receiver_takes_native_publishers_messages():
                 np.testing.assert_array_equal(bbox, want[f]["bbox"])
 
 
-def test_shared_memory_mode_and_the_dataset_host_path():
+@pytest.mark.parametrize("in_place", [False, True])
+def test_shared_memory_mode_and_the_dataset_host_path(in_place):
     """run_native_publishers(shm_slots=N): payloads through shared memory, tickets patched into the pickled
-    template; the datasets' host iteration resolves them like any shared-memory message."""
+    template; the datasets' host iteration resolves them like any shared-memory message.  in_place: the
+    frames stand in their slots (a producer that renders into shared memory), no copy per message."""
     H, W = 64, 96
     binds = ["tcp://127.0.0.1:*"] * 2
     addrs, stop = [], threading.Event()
     th = threading.Thread(target=S.run_native_publishers, args=(binds, [0, 1], 2, H, W),
-                          kwargs=dict(count=-1, pool=4, threads=2, shm_slots=6, ready=addrs.extend, stop=stop))
+                          kwargs=dict(count=-1, pool=4, threads=2, shm_slots=6, ready=addrs.extend, stop=stop, in_place=in_place))
     th.start()
     try:
         t0 = time.time()
