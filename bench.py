@@ -51,6 +51,7 @@ WORKLOAD = "C2: 5 synthetic ZMQ publishers, 640x480 RGBA uint8 + bbox, batch 8, 
 METRIC = "images/sec into device tensors (640x480 RGBA, batch 8)"
 CONFIG_KEYS = {"workload": WORKLOAD, "batch": BATCH, "publishers": PUBLISHERS}   # identical in both arms
 DEVICE_STREAMS = 4  # independent batches in flight in the device leg (one stream per receiver in the pipeline)
+GROUP = None  # DeviceLoader(group=...) of the e2e legs (None = automatic); tools override it
 ROTATE = 8  # distinct resident batches: 8 x (9.8 MB in + 39.3 MB out) = 393 MB > 126 MB L2
 
 
@@ -549,7 +550,7 @@ def stream_leg(ctx, cfg, transport, receivers, senders, shm_slots=0, min_seconds
             pre.append(btt.FlipRows(key="depth"))
         prefetch = 4 if batch <= 64 else 2
         dl = btt.DeviceLoader(ds, batch_size=batch, device=ctx["dev"], preprocess=pre, num_receivers=receivers,
-                              ring_depth=4 if batch <= 64 else 3, prefetch=prefetch, project=project)
+                              ring_depth=4 if batch <= 64 else 3, prefetch=prefetch, project=project, group=GROUP)
         it = iter(dl)
         for _ in range(ctx["warmup"]):
             next(it)["image_stats"].cpu()
@@ -589,7 +590,7 @@ def replay_leg(ctx, cfg, prefix, cache=None, min_seconds=2.0, project=None, dept
         pre.append(btt.FlipRows(key="depth"))
     dl = btt.DeviceLoader(ds, batch_size=batch, shuffle=True, drop_last=True, device=ctx["dev"], preprocess=pre,
                           ingest_threads=threads, ring_depth=3, prefetch=3, num_receivers=producers, cache=cache,
-                          project=project)
+                          project=project, group=GROUP)
     it = None
     try:
         def epochs():
@@ -800,7 +801,7 @@ def ours(args):
         # C1: replay of a recorded Cube-scene stream, 640x480 RGBA + xy, batch 8 (2 files x 512 frames)
         c1 = {"name": "C1", "config": 1, "h": 480, "w": 640, "batch": 8, "pool": 16}
         S.write_recordings(tmp + "/c1", 1, 2, 512, 480, 640, pool=16)
-        rep = replay_leg(ctx, c1, tmp + "/c1", threads=max(1, min(4, len(cpus) - 2)))
+        rep = replay_leg(ctx, c1, tmp + "/c1", threads=max(1, min(8, len(cpus) - 3)))
         barrier()
         rep_host = replay_leg(ctx, c1, tmp + "/c1", cache="host")
         barrier()
@@ -815,7 +816,7 @@ def ours(args):
             S.write_recordings(tmp + "/c3", 3, 2, 64, 1080, 1920, pool=8)
             cam = btt.Camera.from_lens((1080, 1920), lens=35.0, distance=0.0, device=dev)
             pj = btt.Projection("corners", camera=cam, xy_key="corners_xy", bbox_key="boxes", corners_per_object=8)
-            r3 = replay_leg(ctx, c3, tmp + "/c3", project=pj, depth_flip=True, threads=max(1, min(8, len(cpus) - 2)),
+            r3 = replay_leg(ctx, c3, tmp + "/c3", project=pj, depth_flip=True, threads=max(1, min(8, len(cpus) - 3)),
                             min_seconds=1.5)
             barrier()
             r3h = replay_leg(ctx, c3, tmp + "/c3", cache="host", project=pj, depth_flip=True, min_seconds=1.5)

@@ -399,6 +399,10 @@ class DeviceLoader:
         return int(max(1, min(8, -(-self._GROUP_BYTES // per_batch))))
 
     def _group_of_message(self, first_msg, sizes=None):
+        if self.group is None and shm.MARKER_BYTES in bytes(memoryview(first_msg)[:4096]):
+            # payloads by shared-memory reference are copied per item anyway, and a group would hold
+            # its publishers' slots until it is full: with few slots that starves them
+            return 1
         try:
             probe = Schema.from_message(first_msg, 1, sizes, self.allow_pickle)
         except Exception:

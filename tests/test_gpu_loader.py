@@ -215,7 +215,7 @@ def test_config3_depth_and_projection_in_loader(tmp_path):
     S.write_recordings(prefix, config=3, n_files=2, frames_per_file=5, h=H, w=W)
     V, P = ocam.view_looking_down_z(0.0), ocam.blender_perspective((H, W), lens=35.0)
     cam = btt.Camera(V, P, (H, W), device=DEV)
-    dl = btt.DeviceLoader(btt.FileDataset(prefix), batch_size=4, device=DEV,
+    dl = btt.DeviceLoader(btt.FileDataset(prefix), batch_size=4, device=DEV, group=1,
                           preprocess=btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5),
                           project=btt.Projection("corners", cam, xy_key="xy", depth_key="z", bbox_key="bbox"))
     ref = btr.ReplayDataset(prefix)
@@ -237,6 +237,19 @@ def test_config3_depth_and_projection_in_loader(tmp_path):
     # a second epoch reuses the cached pinned ring and gives the same data
     again = [b["frameid"].tolist() for b in dl]
     assert sum(len(x) for x in again) == 10
+    one_by_one = [{k: v.cpu() for k, v in b.items()} for b in dl]
+    dl.close()
+    # the default groups small batches (one copy per column, one K1 and one K2 launch for all three
+    # batches here): same batches, fewer launches
+    dl = btt.DeviceLoader(btt.FileDataset(prefix), batch_size=4, device=DEV,
+                          preprocess=btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5),
+                          project=btt.Projection("corners", cam, xy_key="xy", depth_key="z", bbox_key="bbox"))
+    grouped = [{k: v.cpu() for k, v in b.items()} for b in dl]
+    assert dl.stats["kernels"] == 2 and len(grouped) == len(one_by_one) == 3
+    for a, b in zip(one_by_one, grouped):
+        assert a.keys() == b.keys()
+        for k in a:
+            assert torch.equal(a[k], b[k]), k
     dl.close()
 
 

@@ -31,6 +31,11 @@ def main():
     ap.add_argument("--shm-slots", type=int, default=0)
     ap.add_argument("--python-publishers", action="store_true")
     ap.add_argument("--gpu", type=int, default=0)
+    ap.add_argument("--in-place", action="store_true")
+    ap.add_argument("--replay", nargs="*", default=None, metavar="THREADSxPRODUCERS",
+                    help="replay legs (C1 recording) instead of stream legs, e.g. 4x2 8x2; add --cache-host")
+    ap.add_argument("--cache-host", action="store_true")
+    ap.add_argument("--group", type=int, nargs="+", default=[0], help="DeviceLoader(group=...), 0 = automatic")
     ap.add_argument("--tag", default="")
     a = ap.parse_args()
     cpus = parse_cpus(a.cpus) if a.cpus else sorted(os.sched_getaffinity(0))
@@ -45,9 +50,30 @@ def main():
     ctx = {"torch": torch, "btt": btt, "np": np, "S": S, "N": N, "dev": dev, "rank": a.gpu, "local": a.gpu, "world": 1,
            "cpus": cpus, "steps": 20, "warmup": 5, "sampler": None, "barrier": lambda: torch.cuda.synchronize(dev)}
     c2 = {"name": "C2", "config": 2, "h": bench.H, "w": bench.W, "batch": bench.BATCH, "publishers": bench.PUBLISHERS}
+    if a.replay is not None:
+        import shutil
+        import tempfile
+        tmp = tempfile.mkdtemp(prefix="btrec_sw_", dir="/dev/shm")
+        try:
+            S.write_recordings(tmp + "/c1", 1, 2, 512, 480, 640, pool=16)
+            c1 = {"name": "C1", "config": 1, "h": 480, "w": 640, "batch": 8, "pool": 16}
+            for sp in a.replay or ["4x2"]:
+                th, pr = (int(x) for x in sp.split("x"))
+                for grp in a.group:
+                    bench.GROUP = grp or None
+                    leg = bench.replay_leg(ctx, c1, tmp + "/c1", cache="host" if a.cache_host else None, min_seconds=a.seconds,
+                                           threads=th, producers=pr)
+                    print(json.dumps({"replay": True, "cache": "host" if a.cache_host else None, "ingest_threads": th,
+                                      "producers": pr, "group": grp, "images_per_s": leg["images"] / leg["sec"],
+                                      "GBps": leg["images"] / leg["sec"] * 1228800 / 1e9, "check": leg["check"],
+                                      "consumer_wait_s": leg["consumer_wait_s"]}), flush=True)
+        finally:
+            shutil.rmtree(tmp, ignore_errors=True)
+        return
     for tr in a.transport:
-        for sp in a.split:
+        for sp, grp in ((x, y) for x in a.split for y in a.group):
             s, r = (int(x) for x in sp.split("x"))
+            bench.GROUP = grp or None
             if a.python_publishers:
                 orig = bench.spawn_native_publisher
 
@@ -70,11 +96,11 @@ def main():
                     return addrs, Group()
                 bench.spawn_native_publisher = py
             t0 = time.time()
-            leg = bench.stream_leg(ctx, c2, tr, r, s, shm_slots=a.shm_slots, min_seconds=a.seconds)
+            leg = bench.stream_leg(ctx, c2, tr, r, s, shm_slots=a.shm_slots, min_seconds=a.seconds, in_place=a.in_place)
             if a.python_publishers:
                 bench.spawn_native_publisher = orig
             print(json.dumps({"tag": a.tag, "gpu": a.gpu, "cpus": len(cpus), "transport": tr, "senders": s if not a.python_publishers else "5 python procs",
-                              "receivers": r, "shm_slots": a.shm_slots,
+                              "receivers": r, "shm_slots": a.shm_slots, "in_place": a.in_place, "group": grp,
                               "images_per_s": leg["images"] / leg["sec"], "GBps": leg["images"] / leg["sec"] * 1228800 / 1e9,
                               "consumer_wait_s": leg["consumer_wait_s"], "check": leg["check"], "leg_s": time.time() - t0}), flush=True)
 
