@@ -426,6 +426,9 @@ int bt_flip_rows_launch(const void* src, void* dst, int batch, int height, uint6
  *  - The array costs 76 032 bytes on every GPU that loads the library, until the process exits.
  *  - The first call on each device resolves the array's device address (and, like any first
  *    launch, loads the kernels); make that first call before starting any stream capture.
+ *    The address is remembered per device ordinal for the life of the process: a host that resets
+ *    the device (cudaDeviceReset) or destroys its primary context must reload the library before
+ *    calling this again, because the remembered address belongs to the context that is gone.
  *  - All calls on a device share the one array.  Nothing in it has to start at zero: the partial
  *    sums are written by each call's kernel before its fold reads them, so back-to-back calls on
  *    one stream are fine; calls whose kernels can overlap on the GPU (different streams or

@@ -1114,7 +1114,8 @@ int launch_checked(const bt_preprocess_params* p, void* stream, int stats_rows) 
 //
 // `g_static_stats_scratch` as written in host code is only a host-side handle for the symbol,
 // not a device address; the address a kernel may use is looked up once per device with
-// cudaGetSymbolAddress (that device current) and cached.
+// cudaGetSymbolAddress (that device current) and cached for the life of the process: after a
+// cudaDeviceReset the cached address is stale and the library has to be reloaded (bt_b200.h says so).
 // ---------------------------------------------------------------------------------------------
 #include <mutex>
 

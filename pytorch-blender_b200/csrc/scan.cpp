@@ -365,12 +365,24 @@ bool parse_shape(const Scanner& s, int idx, bt_field* f) {
   return true;
 }
 
+// Number of bytes of an array of `ndim` dimensions `shape` and element size `esize`; false when the
+// product does not fit 64 bits (a crafted shape such as (2^32, 2^32, k) must not wrap around to a
+// small number that then passes a length comparison).
+bool shape_bytes(const int64_t* shape, int ndim, uint64_t esize, uint64_t* out) {
+  uint64_t count = esize;
+  for (int i = 0; i < ndim; ++i) {
+    if (shape[i] < 0) return false;
+    if (__builtin_mul_overflow(count, (uint64_t)shape[i], &count)) return false;
+  }
+  *out = count;
+  return true;
+}
+
 bool finish_array(const Scanner& s, int dtype, int data_idx, bt_field* f) {
   const Node& d = s.nodes[data_idx];
   if (d.k != N_BYTES) return false;
-  uint64_t count = 1;
-  for (int i = 0; i < f->ndim; ++i) count *= (uint64_t)f->shape[i];
-  if (count * (uint64_t)dtype_size(dtype) != d.len) return false;
+  uint64_t nbytes = 0;
+  if (!shape_bytes(f->shape, f->ndim, (uint64_t)dtype_size(dtype), &nbytes) || nbytes != d.len) return false;
   f->kind = BT_KIND_NDARRAY;
   f->dtype = dtype;
   f->payload_off = d.off;
@@ -616,9 +628,10 @@ std::vector<bt_field>& tls_fields() {
 }
 
 uint64_t field_bytes(const bt_field& f) {
-  uint64_t count = 1;
-  for (int i = 0; i < f.ndim; ++i) count *= (uint64_t)f.shape[i];
-  return count * (uint64_t)dtype_size(f.dtype);
+  // ~0 for a shape whose size does not fit 64 bits: equal to no column's item_bytes and to no
+  // payload length, so such a field is rejected wherever sizes are compared
+  uint64_t n = 0;
+  return shape_bytes(f.shape, f.ndim, (uint64_t)dtype_size(f.dtype), &n) ? n : ~0ull;
 }
 
 namespace {
@@ -825,6 +838,13 @@ int bt_schema_create(const uint8_t* first_msg, uint64_t len, int batch, bt_schem
         return fail(BT_E_UNSUPPORTED, "field '%s' (kind %d) has no column representation", fi.key, fi.kind);
     }
     c.slot_off = off;
+    // a slot is one allocation of page-locked memory: refuse layouts that cannot be one (this also
+    // catches field_bytes' ~0 for shapes whose size does not fit 64 bits)
+    constexpr uint64_t kMaxSlot = 1ull << 40;
+    if (c.item_bytes > kMaxSlot / (uint64_t)batch || off + c.item_bytes * (uint64_t)batch > kMaxSlot) {
+      delete s;
+      return fail(BT_E_TOO_LARGE, "field '%s': a batch of %d does not fit a staging slot", fi.key, batch);
+    }
     off = align_up(off + c.item_bytes * (uint64_t)batch, 256);
     s->cols.push_back(c);
   }

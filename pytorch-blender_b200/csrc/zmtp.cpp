@@ -30,6 +30,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
 #include <new>
 #include <string>
 #include <vector>
@@ -79,6 +80,18 @@ struct External {
 thread_local uint64_t g_recv_calls = 0, g_poll_calls = 0;
 
 constexpr int kIoTimeoutMs = 10000;  // a message that started arriving must complete within this
+
+// Largest frame the endpoint accepts.  Sizes come off the wire and go into resize()/reserve(): a
+// garbage or hostile peer must not be able to ask for terabytes.  4 GiB by default (a 1080p RGBA frame
+// with a float32 depth map is 16.6 MB), BT_MAX_MESSAGE_BYTES overrides.
+uint64_t max_frame_bytes() {
+  static const uint64_t v = [] {
+    const char* e = getenv("BT_MAX_MESSAGE_BYTES");
+    const uint64_t n = e ? strtoull(e, nullptr, 10) : 0;
+    return n ? n : (4ull << 30);
+  }();
+  return v;
+}
 
 void close_peer(Peer& p) {
   if (p.fd >= 0) close(p.fd);
@@ -407,7 +420,9 @@ int read_frame_header(Peer& p, int* is_msg, uint64_t* size, int* more) {
     *is_msg = 0;
     return BT_OK;
   }
-  if (sz > (1ull << 40)) return bt::fail(BT_E_IO, "implausible message size");
+  if (sz > max_frame_bytes())
+    return bt::fail(BT_E_IO, "frame of %llu bytes exceeds the limit of %llu (BT_MAX_MESSAGE_BYTES)",
+                    (unsigned long long)sz, (unsigned long long)max_frame_bytes());
   *is_msg = 1;
   *size = sz;
   *more = h[0] & 0x01;
@@ -427,6 +442,7 @@ int read_more_frames(bt_pull* q, Peer& p) {
     if (!is_msg) continue;
     if ((int)q->held_parts.size() >= kMaxParts) return bt::fail(BT_E_IO, "message has more than %d frames", kMaxParts);
     const size_t at = q->held.size();
+    if (at + size > max_frame_bytes()) return bt::fail(BT_E_IO, "message exceeds the size limit (BT_MAX_MESSAGE_BYTES)");
     q->held.resize(at + size);
     rc = take(p, q->held.data() + at, size, kIoTimeoutMs, size <= kAheadBytes);
     if (rc != BT_OK) return rc;
@@ -598,6 +614,7 @@ int receive_raw_parts(bt_pull* q, Peer& p, uint64_t header_size, bt_ring* ring, 
       parts.push_back(Part{size, dst, 0});
     } else {
       const uint64_t at = q->spill.size();
+      if (at + size > max_frame_bytes()) return bt::fail(BT_E_IO, "message exceeds the size limit (BT_MAX_MESSAGE_BYTES)");
       q->spill.resize(at + size);
       rc = take(p, q->spill.data() + at, size, kIoTimeoutMs, size <= kAheadBytes);
       if (rc != BT_OK) return rc;
@@ -647,11 +664,15 @@ int bt_pull_create(bt_pull** out) {
 
 int bt_pull_connect(bt_pull* q, const char* address) {
   if (!q || !address) return bt::fail(BT_E_INVALID, "bt_pull_connect: null argument");
-  Peer p;
-  p.address = address;
-  int rc = parse_address(p.address, p);
-  if (rc != BT_OK) return rc;
-  q->peers.push_back(p);
+  try {
+    Peer p;
+    p.address = address;
+    int rc = parse_address(p.address, p);
+    if (rc != BT_OK) return rc;
+    q->peers.push_back(p);
+  } catch (const std::bad_alloc&) {
+    return bt::fail(BT_E_NOMEM, "out of memory");
+  }
   return BT_OK;
 }
 
@@ -667,8 +688,7 @@ int bt_pull_destroy(bt_pull* q) {
   return BT_OK;
 }
 
-int bt_pull_recv(bt_pull* q, int timeout_ms) {
-  if (!q) return bt::fail(BT_E_INVALID, "null receiver");
+static int pull_recv(bt_pull* q, int timeout_ms) {
   if (q->has_held) return BT_OK;
   const uint64_t deadline = now_ms() + (uint64_t)(timeout_ms < 0 ? 0 : timeout_ms);
   while (true) {
@@ -682,6 +702,19 @@ int bt_pull_recv(bt_pull* q, int timeout_ms) {
     if (rc == BT_OK && is_msg) rc = read_whole(q, p, size, more);
     if (rc != BT_OK) { close_peer(p); continue; }
     if (is_msg) return BT_OK;
+  }
+}
+
+int bt_pull_recv(bt_pull* q, int timeout_ms) {
+  if (!q) return bt::fail(BT_E_INVALID, "null receiver");
+  try {   // sizes off the wire end up in vector::resize: nothing may unwind through the C ABI
+    return pull_recv(q, timeout_ms);
+  } catch (const std::bad_alloc&) {
+    q->has_held = false;
+    return bt::fail(BT_E_NOMEM, "out of memory while receiving a message");
+  } catch (const std::exception& e) {
+    q->has_held = false;
+    return bt::fail(BT_E_NOMEM, "receiving a message failed: %s", e.what());
   }
 }
 
@@ -711,11 +744,28 @@ int bt_pull_drop(bt_pull* q) {
   return BT_OK;
 }
 
+static int pull_fill(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, int first_item, int max_items,
+                     int slice_ms, int* n_done);
+
 int bt_pull_fill(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, int first_item, int max_items,
                  int slice_ms, int* n_done) {
   if (!q || !ring || !schema || !n_done || first_item < 0 || max_items < 0 || first_item + max_items > schema->batch)
     return bt::fail(BT_E_INVALID, "bt_pull_fill: bad arguments");
+  // payloads are received straight into the slot: it has to exist and to hold the schema's layout
+  if (slot < 0 || slot >= bt_ring_depth(ring) || schema->slot_bytes > bt_ring_slot_bytes(ring))
+    return bt::fail(BT_E_INVALID, "bt_pull_fill: slot %d is outside the ring, or the ring's slots are smaller than the schema", slot);
   *n_done = 0;
+  try {
+    return pull_fill(q, ring, slot, schema, first_item, max_items, slice_ms, n_done);
+  } catch (const std::bad_alloc&) {
+    return bt::fail(BT_E_NOMEM, "out of memory while receiving a message");
+  } catch (const std::exception& e) {
+    return bt::fail(BT_E_NOMEM, "receiving a message failed: %s", e.what());
+  }
+}
+
+static int pull_fill(bt_pull* q, bt_ring* ring, int slot, const bt_schema* schema, int first_item, int max_items,
+                     int slice_ms, int* n_done) {
   while (*n_done < max_items) {
     if (q->has_held) {  // the first message of the stream, received before the schema existed
       int rc = ingest_held(q, ring, slot, schema, first_item + *n_done);

@@ -208,3 +208,29 @@ def test_gamma_lut_matches_oracle(golden_dir):
         np.testing.assert_array_equal(lut, tabs[name])
     for g in (1.1, 1.5, 2.6, 3.0, 0.7):
         np.testing.assert_array_equal(np.frombuffer(N.gamma_lut(g), np.uint8), preprocess.gamma_table(g))
+
+
+def test_shapes_whose_size_overflows_are_rejected_not_wrapped():
+    """a crafted shape such as (2**32, 2**32, 3) multiplies to a small number modulo 2**64; it
+    must not pass the payload-length comparison and become a schema column."""
+    import pickle
+    import numpy as np
+    from blendtorch.btt import native as N
+    from blendtorch.btt.staging import Schema
+    good = pickle.dumps({"btid": 0, "image": np.zeros((2, 2, 3), np.uint8)}, protocol=3)
+    def ints(dims):                                          # the opcodes that push the integers of a shape
+        return b"".join(pickle.dumps(d, protocol=3)[2:-1] for d in dims)
+    shape = ints((2, 2, 3)) + b"\x87"                          # ... followed by TUPLE3
+    assert good.count(shape) == 1
+    for dims in ((2 ** 32, 2 ** 32, 3), (2 ** 63 - 1, 2, 6), (2 ** 62, 4, 3)):
+        bad = good.replace(shape, ints(dims) + b"\x87")
+        f = {x.key.decode(): x for x in N.scan_message(bad)}
+        assert f["image"].kind == N.BT_KIND_OTHER            # not an array the native path will touch
+        h = __import__("ctypes").c_void_p()
+        addr, n = N.buffer_address(bad)
+        assert N.lib.bt_schema_create(addr, n, 8, __import__("ctypes").byref(h)) == N.BT_E_UNSUPPORTED
+    # a marker (no payload to compare with) whose shape overflows cannot become a column
+    huge = pickle.dumps({"btid": 0, "image": ("__btraw__", 1, "|u1", (2 ** 40, 2 ** 40))}, protocol=3)
+    h = __import__("ctypes").c_void_p()
+    addr, n = N.buffer_address(huge)
+    assert N.lib.bt_schema_create(addr, n, 8, __import__("ctypes").byref(h)) == N.BT_E_TOO_LARGE
