@@ -370,8 +370,10 @@ typedef struct bt_preprocess_params {
   int32_t use_norm;       /* ignored for BT_U8 output */
   int32_t variant;        /* 0 = auto, 1 = generic scalar (one value per thread), 2 = register-vectorised
                              (fails if rows are not whole vector units), 3 = bulk-async (cp.async.bulk + mbarrier ring)
-                             staged input for RGBA planar output, kept as the measured A/B of 2; auto may also pick the
-                             pixel-per-thread kernel, reported as 4 by bt_preprocess_last_variant() */
+                             staged input for RGBA planar output, kept as the measured A/B of 2; 4 = one pixel per
+                             thread (any width); auto may also pick, for RGBA rows of any width and planar output, the
+                             kernel that stores aligned groups of four plane elements, reported as 5 by
+                             bt_preprocess_last_variant() */
   int32_t reserved;       /* 0; developer tuning knob (units per thread | CTAs-per-SM cap << 8) */
   uint64_t src_image_stride; /* bytes between consecutive images in src; 0 = dense */
   float mean[4];

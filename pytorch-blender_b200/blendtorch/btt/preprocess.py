@@ -15,7 +15,7 @@ import torch
 from . import native as N
 
 _TORCH_OUT = {torch.uint8: N.BT_U8, torch.float32: N.BT_F32, torch.bfloat16: N.BT_BF16}
-VARIANTS = {"auto": 0, "generic": 1, "vector": 2, "bulk": 3}
+VARIANTS = {"auto": 0, "generic": 1, "vector": 2, "bulk": 3, "pixel": 4}
 
 
 def _per_channel(v, default):

@@ -42,6 +42,13 @@ struct K1Args {
   uint8_t gamma_lut[256];
   double* partials;       // [gridDim.x][kMaxC][2] when stats are on
   double* stats_out;      // [Cout][2]
+  // The 4 x 256 possible outputs, made on the host by the launcher with the reference's expression
+  // (IEEE float subtract and divide give the same bits on the host as __fsub_rn/__fdiv_rn on the
+  // device) and carried as kernel parameters: every CTA copies them into shared memory instead of
+  // repeating four IEEE divisions per thread.  At one 16-byte unit per thread -- the shape of a batch-8
+  // launch -- those divisions were close to half of the kernel's instructions.
+  uint32_t table[kMaxC * 256];   // kMaxC*256 values of the output type, packed
+  uint32_t has_table;
 };
 
 // Byte offset of the source image that feeds batch item `b`: dense batches read image b, gathered
@@ -71,6 +78,15 @@ template <> struct OutT<uint8_t> {
 template <typename T>
 __device__ __forceinline__ void build_lut(const K1Args& a, T* lut /* [kMaxC][256] */) {
   static_assert(kThreads == 256, "one thread per table index");
+  if (a.has_table) {
+    // host-built table: thread t copies words t, t+256, ... (consecutive lanes, consecutive banks)
+    constexpr int kWords = kMaxC * 256 * (int)sizeof(T) / 4;
+    uint32_t* dst = reinterpret_cast<uint32_t*>(lut);
+#pragma unroll
+    for (int k = 0; k < kWords / kThreads; ++k) dst[threadIdx.x + k * kThreads] = a.table[threadIdx.x + k * kThreads];
+    __syncthreads();
+    return;
+  }
   // Thread v makes entry v of every channel.  The gamma byte is read once, as the 32-bit word that
   // holds it (a warp touches 8 distinct words of the parameter bank instead of 32 distinct bytes),
   // and the channel loop is unrolled so that mean/stdev are plain constant operands.
@@ -225,7 +241,7 @@ __device__ void finish_stats(const K1Args& a, StatAcc& acc) {
 
 // ---- variant 1: generic scalar (any shape) -----------------------------------------------
 template <typename T, bool CHW, bool STATS>
-__global__ void __launch_bounds__(kThreads) k1_generic(K1Args a) {
+__global__ void __launch_bounds__(kThreads) k1_generic(const __grid_constant__ K1Args a) {
   __shared__ T lut[kMaxC * 256];
   build_lut<T>(a, lut);
   StatAcc acc;
@@ -287,7 +303,7 @@ __device__ __forceinline__ void ld_words(const uint8_t* p, uint32_t* w) {
 }
 
 template <typename T, int C, int PPT, int UNROLL, bool STATS>
-__global__ void __launch_bounds__(kThreads, (STATS || sizeof(T) == 2) ? 4 : 0) k1_planar(K1Args a, PlanarGeom g) {
+__global__ void __launch_bounds__(kThreads, (STATS || sizeof(T) == 2) ? 4 : 0) k1_planar(const __grid_constant__ K1Args a, PlanarGeom g) {
   constexpr int UB = PPT * C;                              // unit bytes
   constexpr int LW = (UB % 16 == 0) ? 16 : (UB % 8 == 0) ? 8 : 4;
   static_assert(UB % 4 == 0, "unit must be whole 32-bit words");
@@ -411,7 +427,7 @@ struct BulkGeom {
 };
 
 template <typename T>
-__global__ void __launch_bounds__(kThreads) k1_bulk(K1Args a, BulkGeom g) {
+__global__ void __launch_bounds__(kThreads) k1_bulk(const __grid_constant__ K1Args a, BulkGeom g) {
   __shared__ __align__(128) uint8_t stage[kBulkStages][kBulkSegBytes];
   __shared__ __align__(8) uint64_t full[kBulkStages];
   __shared__ T lut[kMaxC * 256];
@@ -497,7 +513,7 @@ __global__ void __launch_bounds__(kThreads) k1_bulk(K1Args a, BulkGeom g) {
 // instruction (fp32: 4 bytes in -> float4 out; bf16: 8 -> 16; u8: 16 -> 16).  Needs Cout == C.
 // IDENT (u8 without gamma) skips the table: the kernel is then a flipping copy.
 template <typename T, int UNROLL, bool STATS, bool IDENT, int CFIX>
-__global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a, PlanarGeom g) {
+__global__ void __launch_bounds__(kThreads) k1_interleaved(const __grid_constant__ K1Args a, PlanarGeom g) {
   constexpr int IB = 16 / (int)sizeof(T);
   constexpr int LW = IB;  // one load per unit
   __shared__ T lut[kMaxC * 256];
@@ -573,7 +589,7 @@ __global__ void __launch_bounds__(kThreads) k1_interleaved(K1Args a, PlanarGeom 
 // (a 32-bit load for C == 4, byte loads otherwise) and writes C_out scalars; lanes are consecutive
 // pixels, so planar stores are 128 contiguous bytes per warp instruction and loads are dense.
 template <typename T, int C, bool CHW, int UNROLL, bool STATS>
-__global__ void __launch_bounds__(kThreads) k1_pixel(K1Args a, PlanarGeom g) {
+__global__ void __launch_bounds__(kThreads) k1_pixel(const __grid_constant__ K1Args a, PlanarGeom g) {
   __shared__ T lut[kMaxC * 256];
   const bool loads_first = (a.flags & 1u) != 0;   // as in k1_planar: the table build hides under the first loads
   if (!loads_first) build_lut<T>(a, lut);
@@ -628,6 +644,82 @@ __global__ void __launch_bounds__(kThreads) k1_pixel(K1Args a, PlanarGeom g) {
           else dst[off] = o;
           if (STATS) { float f = OutT<T>::as_float(o); acc.s[c] += f; acc.q[c] += (double)f * f; }
         }
+      }
+    }
+  }
+  if (STATS) finish_stats(a, acc);
+}
+
+// ---- variant 2d: RGBA of any width, planar output, aligned vector stores ---------------------------
+// Widths that are not a multiple of 4 leave neither the input rows nor the output plane rows on
+// 16-byte boundaries, and with a flip the two are out of step with each other.  k1_pixel answers with
+// one pixel and four scalar stores per thread (instruction-bound: 0.5-0.6 of the HBM peak).  Here the
+// work is cut along the *output* instead: the image of item b is H*W pixels back to back and so is each
+// of its planes, so a unit is one aligned group of four plane elements -- one vector store per channel
+// -- whatever row they belong to.  Plane c of item b starts ((b*Cout + c)*H*W) elements into the
+// output, i.e. d_c = that mod 4 elements past a boundary: thread k of an image handles, for channel c,
+// the elements [4k - d_c, 4k - d_c + 4), which lie among the seven pixels 4k-3 .. 4k+3.  Those are read
+// with seven 32-bit loads (through L1: neighbouring threads share them), each from wherever its row
+// is in the -- possibly flipped -- source.  Every element is stored exactly once; groups that stick out
+// of the plane at either end store their valid elements one by one.
+template <typename T, bool STATS>
+__global__ void __launch_bounds__(kThreads) k1_window(const __grid_constant__ K1Args a, PlanarGeom g) {
+  __shared__ T lut[kMaxC * 256];
+  build_lut<T>(a, lut);
+  StatAcc acc;
+  if (STATS) acc.clear();
+  const uint32_t plane = a.H * a.W;                        // < 2^30 (checked by the launcher)
+  T* dst = static_cast<T*>(a.dst);
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t u = blockIdx.x * blockDim.x + threadIdx.x; u < g.total_units; u += stride) {
+    const uint32_t b = fdiv(u, g.rows);                    // g.rows: groups per image
+    const uint32_t k = u - b * g.rows.div;
+    const uint8_t* img = a.src + src_image_off(a, b);
+    // the seven pixels 4k-3 .. 4k+3 (those inside the image), row and column kept incrementally
+    uint32_t px[7];
+    const int first = (int)(4 * k) - 3;
+    int i0 = first < 0 ? 0 : first;
+    uint32_t y = fdiv((uint32_t)i0, g.upr), x = (uint32_t)i0 - y * g.upr.div;   // g.upr: W
+#pragma unroll
+    for (int j = 0; j < 7; ++j) {
+      const int i = first + j;
+      px[j] = 0;
+      if (i >= i0 && (uint32_t)i < plane) {
+        const uint32_t sy = a.flip ? a.H - 1 - y : y;
+        px[j] = __ldg(reinterpret_cast<const unsigned int*>(img + ((uint64_t)sy * a.W + x) * 4));
+        if (++x == a.W) { x = 0; ++y; }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      if (c < (int)a.Cout) {
+        const uint64_t plane_off = ((uint64_t)b * a.Cout + c) * plane;
+        const int d = (int)(plane_off & 3);
+        const int e0 = (int)(4 * k) - d;                   // first element of this thread's group, plane-local
+        T vals[4];
+        float fs = 0.f, fq = 0.f;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          // element e0 + t is pixel 4k - d + t = window slot 3 - d + t; d is one of 0..3
+          const uint32_t w = d == 0 ? px[3 + t] : d == 1 ? px[2 + t] : d == 2 ? px[1 + t] : px[t];
+          const uint32_t v = (w >> (8 * c)) & 0xffu;
+          if (sizeof(T) == 1 && c == 3) vals[t] = OutT<T>::make((float)v, (uint8_t)v);   // alpha passes through
+          else vals[t] = lut[c * 256 + v];
+          if (STATS && e0 + t >= 0 && (uint32_t)(e0 + t) < plane) {
+            const float f = OutT<T>::as_float(vals[t]);
+            fs += f;
+            fq = fmaf(f, f, fq);
+          }
+        }
+        T* out = dst + plane_off + e0;
+        if (e0 >= 0 && (uint32_t)e0 + 4 <= plane) {
+          st_stream<T, 4>(out, vals);
+        } else {
+#pragma unroll
+          for (int t = 0; t < 4; ++t)
+            if (e0 + t >= 0 && (uint32_t)(e0 + t) < plane) out[t] = vals[t];
+        }
+        if (STATS) { acc.s[c] += (double)fs; acc.q[c] += (double)fq; }
       }
     }
   }
@@ -762,7 +854,7 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
   const uint64_t rows = (uint64_t)a.B * a.H;
   const bool aligned_src = (reinterpret_cast<uintptr_t>(a.src) % 16 == 0) && (a.src_image_stride % 16 == 0);
   const bool aligned_dst = reinterpret_cast<uintptr_t>(a.dst) % 16 == 0;
-  const bool can_vec = aligned_src && aligned_dst && variant != 1;
+  const bool can_vec = aligned_src && aligned_dst && variant != 1 && variant != 4;
   const int tune_ctas = (p->reserved >> 8) & 0xff;
   auto grid_of = [&](uint64_t units, int unroll, int resident = 0) {
     int g = grid_for((units + unroll - 1) / unroll, sms, tune_ctas ? tune_ctas : kDefaultCtasPerSm);
@@ -867,6 +959,23 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
   }
   if (variant == 2 || variant == 3)
     return bt::fail(BT_E_INVALID, "requested vectorised variant needs rows made of whole 16-byte units (W=%u C=%u)", a.W, a.C);
+  if (variant != 1 && variant != 4 && p->chw && a.C == 4 && aligned_dst &&
+      reinterpret_cast<uintptr_t>(a.src) % 4 == 0 && a.src_image_stride % 4 == 0) {
+    // RGBA rows of any width, planar output: aligned groups of four plane elements (k1_window)
+    const uint64_t plane = (uint64_t)a.H * a.W;
+    const uint64_t groups = (plane + 3) / 4 + 1;           // d_c <= 3 can push one more group into the plane
+    const uint64_t total = groups * a.B;
+    if (plane < (1ull << 30) && total < (1ull << 31)) {
+      PlanarGeom geo;
+      geo.upr = make_fastdiv(a.W);
+      geo.rows = make_fastdiv((uint32_t)groups);
+      geo.total_units = (uint32_t)total;
+      int g = grid_of(total, 1);
+      k1_window<T, STATS><<<g, kThreads, 0, st>>>(a, geo);
+      g_last_variant = 5;
+      return g;
+    }
+  }
   if (variant != 1) {
     // any width: one pixel per thread
     PlanarGeom geo;
@@ -1010,6 +1119,59 @@ int bt_preprocess_launch(const bt_preprocess_params* p, void* stream) { return l
 
 namespace {
 
+// The table of all possible outputs (K1Args::table), computed with the reference's expression in IEEE
+// float arithmetic -- the host's subtract and divide round exactly like __fsub_rn / __fdiv_rn -- and
+// remembered per thread: consecutive launches of a pipeline use the same transform.
+void fill_table(K1Args& a, int out_dtype, bool enable) {
+  a.has_table = 0;
+  if (!enable) return;
+  struct Key {
+    int out_dtype;
+    uint32_t use_gamma, use_norm;
+    float mean[4], stdev[4];
+    uint8_t gamma[256];
+  };
+  thread_local Key last_key;
+  thread_local uint32_t last_table[kMaxC * 256];
+  thread_local bool have = false;
+  Key key;
+  memset(&key, 0, sizeof key);
+  key.out_dtype = out_dtype;
+  key.use_gamma = a.use_gamma;
+  key.use_norm = a.use_norm;
+  memcpy(key.mean, a.mean, sizeof key.mean);
+  memcpy(key.stdev, a.stdev, sizeof key.stdev);
+  if (a.use_gamma) memcpy(key.gamma, a.gamma_lut, 256);
+  if (!have || memcmp(&key, &last_key, sizeof key) != 0) {
+    memset(last_table, 0, sizeof last_table);
+    for (int c = 0; c < kMaxC; ++c) {
+      for (int v = 0; v < 256; ++v) {
+        const uint32_t g = a.use_gamma ? a.gamma_lut[v] : (uint32_t)v;
+        const uint32_t gc = c < 3 ? g : (uint32_t)v;   // alpha is never gamma-corrected (offscreen.py:109-111)
+        volatile float o = (float)gc;                  // volatile: each step is rounded to float, nothing is fused
+        if (a.use_norm) {
+          volatile float d = o - a.mean[c];
+          o = d / a.stdev[c];
+        }
+        const int i = c * 256 + v;
+        if (out_dtype == BT_F32) {
+          const float f = o;
+          memcpy(&last_table[i], &f, 4);
+        } else if (out_dtype == BT_BF16) {
+          const __nv_bfloat16 h = __float2bfloat16_rn((float)o);
+          memcpy(reinterpret_cast<uint8_t*>(last_table) + 2 * i, &h, 2);
+        } else {
+          reinterpret_cast<uint8_t*>(last_table)[i] = (uint8_t)gc;
+        }
+      }
+    }
+    last_key = key;
+    have = true;
+  }
+  memcpy(a.table, last_table, sizeof a.table);
+  a.has_table = 1;
+}
+
 // `stats_rows`: how many partial-sum rows `p->stats_scratch` has room for (bounds the grid).
 int launch_checked(const bt_preprocess_params* p, void* stream, int stats_rows) {
   if (!p || !p->src || !p->dst) return bt::fail(BT_E_INVALID, "bt_preprocess_launch: null pointer");
@@ -1044,6 +1206,7 @@ int launch_checked(const bt_preprocess_params* p, void* stream, int stats_rows) 
     for (int c = 0; c < p->channels; ++c)
       if (a.stdev[c] == 0.0f) return bt::fail(BT_E_INVALID, "stdev[%d] is zero", c);
 
+  fill_table(a, p->out_dtype, ((p->reserved >> 19) & 1) == 0);   // tuning bit 19: build the table on the device instead
   const bool stats = p->stats_out != nullptr;
   double* group_rows = nullptr;
   if (stats) {

@@ -112,9 +112,20 @@ def main():
                   for n in ((1, 2, 4) if sh == C2 else (1,))]
         cases += [dict(shape=C2, dtype=torch.float32, variant=v, streams=n) for v in ("bulk",) for n in (1, 2, 4)]
         cases += [dict(shape=C4, dtype=torch.float32, variant="bulk")]
+    elif len(sys.argv) > 1 and sys.argv[1] == "table":
+        # host-built table in kernel parameters (default) against the table built by every CTA (bit 19)
+        cases = [dict(shape=sh, dtype=dt, tune=t, streams=n, stats=st) for sh in (C2, (16, 480, 640, 4), C5, C4)
+                 for dt in (torch.float32, torch.bfloat16) for st in (False, True) for t in (0, 0x80000)
+                 for n in ((1, 4) if sh[0] <= 16 else (1,))] * 2
+        cases += [dict(shape=C4, dtype=torch.uint8, layout="NHWC", tune=t) for t in (0, 0x80000)]
+        cases += [dict(shape=sh, dtype=torch.float32, layout="NHWC", tune=t) for sh in (C2, C4) for t in (0, 0x80000)]
     elif len(sys.argv) > 1 and sys.argv[1] == "odd":
-        cases = [dict(shape=sh, dtype=dt, tune=t, streams=n) for sh in ((8, 481, 641, 4), (64, 481, 641, 4), (8, 481, 641, 3))
-                 for dt in (torch.float32, torch.bfloat16) for t in (0, 0x40000) for n in (1, 4)] * 2
+        # odd widths: aligned plane groups (auto, k1_window) against one pixel per thread (k1_pixel)
+        cases = [dict(shape=sh, dtype=dt, variant=v, streams=n, stats=st)
+                 for sh in ((8, 481, 641, 4), (64, 481, 641, 4), (32, 1080, 1918, 4), (64, 1023, 1022, 4))
+                 for dt in (torch.float32, torch.bfloat16) for st in (False, True) for v in ("auto", "pixel")
+                 for n in ((1, 4) if sh[0] == 8 else (1,))]
+        cases += [dict(shape=(64, 481, 641, 4), dtype=torch.uint8, variant=v) for v in ("auto", "pixel")]
     elif len(sys.argv) > 1 and sys.argv[1] == "nhwc_lf":
         cases = [dict(shape=sh, dtype=dt, layout="NHWC", tune=t, streams=n) for sh in (C2, (64, 480, 640, 4), C5, C4)
                  for dt in (torch.float32, torch.uint8, torch.bfloat16) for t in (0, 0x40000)
