@@ -42,11 +42,9 @@ struct K1Args {
   uint8_t gamma_lut[256];
   double* partials;       // [gridDim.x][kMaxC][2] when stats are on
   double* stats_out;      // [Cout][2]
-  // The 4 x 256 possible outputs, made on the host by the launcher with the reference's expression
-  // (IEEE float subtract and divide give the same bits on the host as __fsub_rn/__fdiv_rn on the
-  // device) and carried as kernel parameters: every CTA copies them into shared memory instead of
-  // repeating four IEEE divisions per thread.  At one 16-byte unit per thread -- the shape of a batch-8
-  // launch -- those divisions were close to half of the kernel's instructions.
+  // Optional (tuning bit 19, an A/B that lost: see launch_checked): the 4 x 256 possible outputs made on
+  // the host with the reference's expression and carried as kernel parameters, for the CTAs to copy
+  // instead of computing them.
   uint32_t table[kMaxC * 256];   // kMaxC*256 values of the output type, packed
   uint32_t has_table;
 };
@@ -662,6 +660,34 @@ __global__ void __launch_bounds__(kThreads) k1_pixel(const __grid_constant__ K1A
 // with seven 32-bit loads (through L1: neighbouring threads share them), each from wherever its row
 // is in the -- possibly flipped -- source.  Every element is stored exactly once; groups that stick out
 // of the plane at either end store their valid elements one by one.
+// One aligned group of four elements of plane c, taken from window slots OFF .. OFF+3 (OFF = 3 - d_c).
+template <typename T, bool STATS, int OFF>
+__device__ __forceinline__ void window_emit(const uint32_t (&px)[7], const T* lut, int c, T* out, int e0, uint32_t plane,
+                                            double& s, double& q) {
+  T vals[4];
+  float fs = 0.f, fq = 0.f;
+  const bool whole = e0 >= 0 && (uint32_t)e0 + 4 <= plane;
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const uint32_t v = (px[OFF + t] >> (8 * c)) & 0xffu;
+    if (sizeof(T) == 1 && c == 3) vals[t] = OutT<T>::make((float)v, (uint8_t)v);   // alpha passes through
+    else vals[t] = lut[c * 256 + v];
+    if (STATS && (whole || (e0 + t >= 0 && (uint32_t)(e0 + t) < plane))) {
+      const float f = OutT<T>::as_float(vals[t]);
+      fs += f;
+      fq = fmaf(f, f, fq);
+    }
+  }
+  if (whole) {
+    st_stream<T, 4>(out, vals);
+  } else {
+#pragma unroll
+    for (int t = 0; t < 4; ++t)
+      if (e0 + t >= 0 && (uint32_t)(e0 + t) < plane) out[t] = vals[t];
+  }
+  if (STATS) { s += (double)fs; q += (double)fq; }
+}
+
 template <typename T, bool STATS>
 __global__ void __launch_bounds__(kThreads) k1_window(const __grid_constant__ K1Args a, PlanarGeom g) {
   __shared__ T lut[kMaxC * 256];
@@ -675,51 +701,42 @@ __global__ void __launch_bounds__(kThreads) k1_window(const __grid_constant__ K1
     const uint32_t b = fdiv(u, g.rows);                    // g.rows: groups per image
     const uint32_t k = u - b * g.rows.div;
     const uint8_t* img = a.src + src_image_off(a, b);
-    // the seven pixels 4k-3 .. 4k+3 (those inside the image), row and column kept incrementally
+    // the seven pixels 4k-3 .. 4k+3 (those inside the image)
     uint32_t px[7];
     const int first = (int)(4 * k) - 3;
-    int i0 = first < 0 ? 0 : first;
+    const int i0 = first < 0 ? 0 : first;
     uint32_t y = fdiv((uint32_t)i0, g.upr), x = (uint32_t)i0 - y * g.upr.div;   // g.upr: W
+    if (first >= 0 && x + 7 <= a.W && (uint32_t)first + 7 <= plane) {
+      // the usual case: all seven in one row, i.e. 28 consecutive bytes of the source
+      const uint32_t sy = a.flip ? a.H - 1 - y : y;
+      const unsigned int* sp = reinterpret_cast<const unsigned int*>(img + ((uint64_t)sy * a.W + x) * 4);
 #pragma unroll
-    for (int j = 0; j < 7; ++j) {
-      const int i = first + j;
-      px[j] = 0;
-      if (i >= i0 && (uint32_t)i < plane) {
-        const uint32_t sy = a.flip ? a.H - 1 - y : y;
-        px[j] = __ldg(reinterpret_cast<const unsigned int*>(img + ((uint64_t)sy * a.W + x) * 4));
-        if (++x == a.W) { x = 0; ++y; }
+      for (int j = 0; j < 7; ++j) px[j] = __ldg(sp + j);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 7; ++j) {
+        const int i = first + j;
+        px[j] = 0;
+        if (i >= i0 && (uint32_t)i < plane) {
+          const uint32_t sy = a.flip ? a.H - 1 - y : y;
+          px[j] = __ldg(reinterpret_cast<const unsigned int*>(img + ((uint64_t)sy * a.W + x) * 4));
+          if (++x == a.W) { x = 0; ++y; }
+        }
       }
     }
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
       if (c < (int)a.Cout) {
         const uint64_t plane_off = ((uint64_t)b * a.Cout + c) * plane;
-        const int d = (int)(plane_off & 3);
+        const int d = (int)(plane_off & 3);                // the same for every thread on this image: no divergence
         const int e0 = (int)(4 * k) - d;                   // first element of this thread's group, plane-local
-        T vals[4];
-        float fs = 0.f, fq = 0.f;
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          // element e0 + t is pixel 4k - d + t = window slot 3 - d + t; d is one of 0..3
-          const uint32_t w = d == 0 ? px[3 + t] : d == 1 ? px[2 + t] : d == 2 ? px[1 + t] : px[t];
-          const uint32_t v = (w >> (8 * c)) & 0xffu;
-          if (sizeof(T) == 1 && c == 3) vals[t] = OutT<T>::make((float)v, (uint8_t)v);   // alpha passes through
-          else vals[t] = lut[c * 256 + v];
-          if (STATS && e0 + t >= 0 && (uint32_t)(e0 + t) < plane) {
-            const float f = OutT<T>::as_float(vals[t]);
-            fs += f;
-            fq = fmaf(f, f, fq);
-          }
-        }
         T* out = dst + plane_off + e0;
-        if (e0 >= 0 && (uint32_t)e0 + 4 <= plane) {
-          st_stream<T, 4>(out, vals);
-        } else {
-#pragma unroll
-          for (int t = 0; t < 4; ++t)
-            if (e0 + t >= 0 && (uint32_t)(e0 + t) < plane) out[t] = vals[t];
+        switch (d) {
+          case 0: window_emit<T, STATS, 3>(px, lut, c, out, e0, plane, acc.s[c], acc.q[c]); break;
+          case 1: window_emit<T, STATS, 2>(px, lut, c, out, e0, plane, acc.s[c], acc.q[c]); break;
+          case 2: window_emit<T, STATS, 1>(px, lut, c, out, e0, plane, acc.s[c], acc.q[c]); break;
+          default: window_emit<T, STATS, 0>(px, lut, c, out, e0, plane, acc.s[c], acc.q[c]); break;
         }
-        if (STATS) { acc.s[c] += (double)fs; acc.q[c] += (double)fq; }
       }
     }
   }
@@ -1206,7 +1223,13 @@ int launch_checked(const bt_preprocess_params* p, void* stream, int stats_rows) 
     for (int c = 0; c < p->channels; ++c)
       if (a.stdev[c] == 0.0f) return bt::fail(BT_E_INVALID, "stdev[%d] is zero", c);
 
-  fill_table(a, p->out_dtype, ((p->reserved >> 19) & 1) == 0);   // tuning bit 19: build the table on the device instead
+  // A/B kept for the record (tuning bit 19; profiles/r2_k1_table_ab.txt): handing every CTA the finished
+  // table as 4 KB of kernel parameters instead of letting it compute the table.  It loses badly for
+  // fp32 -- 25.7 vs 9.5 us at batch 8, 154 vs 52 us at 1024 x 128^2 -- because the copy out of the
+  // parameter bank is an LDC with a different address in every lane, which the constant cache serves
+  // one address at a time (four such loads per thread for fp32, two for bf16: -5 %, one for uint8: +1 %).
+  // Four IEEE divisions per thread, hidden under the first loads' DRAM latency, are cheaper.
+  fill_table(a, p->out_dtype, ((p->reserved >> 19) & 1) != 0);
   const bool stats = p->stats_out != nullptr;
   double* group_rows = nullptr;
   if (stats) {

@@ -117,6 +117,28 @@ def test_variants_agree_and_vector_path_is_taken():
         _run(rng.integers(0, 256, (1, 4, 5, 4), dtype=np.uint8), variant="vector")
 
 
+def test_odd_widths_take_the_aligned_group_kernel_and_agree_with_the_oracle():
+    """RGBA rows whose width is not a multiple of 4 (neither input rows nor plane rows are 16-byte
+    aligned): planar output goes through k1_window (variant 5); same bits as the oracle, as one pixel per
+    thread and as the scalar kernel, for flips, dropped alpha, every output type and images whose plane
+    size leaves every alignment phase (H*W mod 4 = 1, 2, 3) and whose windows straddle rows."""
+    from blendtorch.btt import native as N
+    rng = np.random.default_rng(11)
+    for shape in ((3, 37, 101, 4), (2, 5, 3, 4), (4, 9, 6, 4), (5, 1, 7, 4), (2, 3, 1, 4), (1, 1, 1, 4), (3, 13, 1022, 4)):
+        frames = rng.integers(0, 256, shape, dtype=np.uint8)
+        for dtype, flip, oc in itertools.product((torch.float32, torch.bfloat16, torch.uint8), (False, True), (None, 3)):
+            kw = dict(flip=flip, gamma=2.2, dtype=dtype, out_channels=oc)
+            if dtype != torch.uint8:
+                kw.update(mean=[100.0, 110.0, 120.0, 130.0], std=[50.0, 60.0, 70.0, 80.0])
+            got = _run(frames, **kw)
+            assert N.lib.bt_preprocess_last_variant() == 5
+            _assert_matches(got, _oracle(frames, flip, 2.2, kw.get("mean"), kw.get("std"), "NCHW", dtype, oc), dtype)
+            px = _run(frames, variant="pixel", **kw)
+            assert N.lib.bt_preprocess_last_variant() == 4
+            assert torch.equal(got.view(torch.uint8), px.view(torch.uint8))
+            assert torch.equal(got.view(torch.uint8), _run(frames, variant="generic", **kw).view(torch.uint8))
+
+
 def test_stats_match_oracle_and_are_deterministic():
     rng = np.random.default_rng(9)
     frames = rng.integers(0, 256, (6, 40, 64, 4), dtype=np.uint8)
@@ -130,10 +152,16 @@ def test_stats_match_oracle_and_are_deterministic():
         np.testing.assert_allclose(got[:, 1], q, rtol=1e-6, atol=1e-3)
         out2, st2 = _run(frames, stats=True, **kw)
         assert torch.equal(st, st2)                                        # fixed reduction order
-    # generic variant too
-    out, st = _run(frames[:, :, :5], stats=True, mean=127.5, std=127.5)
+    # generic variant too (every value goes straight into a float64 sum)
+    out, st = _run(frames[:, :, :5], stats=True, mean=127.5, std=127.5, variant="generic")
     s, q = opre.batch_stats(out.cpu().numpy())
     np.testing.assert_allclose(st.cpu().numpy()[:, 0], s, rtol=1e-9, atol=1e-6)
+    # odd widths: the aligned-group kernel (fp32 partial sums of 4 values) and one pixel per thread
+    for variant in ("auto", "pixel"):
+        out, st = _run(frames[:, :, :5], stats=True, mean=127.5, std=127.5, variant=variant)
+        s, q = opre.batch_stats(out.cpu().numpy())
+        np.testing.assert_allclose(st.cpu().numpy()[:, 0], s, rtol=1e-6, atol=1e-3)
+        np.testing.assert_allclose(st.cpu().numpy()[:, 1], q, rtol=1e-6, atol=1e-3)
 
 
 def test_empty_and_strided_batches():
@@ -219,7 +247,7 @@ def test_gather_index_matches_oracle_on_every_variant():
     from blendtorch.btt import native as N
     rng = np.random.default_rng(33)
     cases = [((9, 12, 16, 4), "auto", 2), ((9, 12, 16, 4), "generic", 1), ((6, 8, 1028, 4), "bulk", 3),
-             ((7, 7, 5, 4), "auto", 4), ((5, 9, 16, 3), "auto", None), ((4, 5, 16, 1), "auto", None)]
+             ((7, 7, 5, 4), "auto", None), ((7, 7, 5, 4), "pixel", 4), ((5, 9, 16, 3), "auto", None), ((4, 5, 16, 1), "auto", None)]
     for shape, variant, ran in cases:
         frames = rng.integers(0, 256, shape, dtype=np.uint8)
         src = torch.from_numpy(frames).to(DEV)
@@ -236,6 +264,8 @@ def test_gather_index_matches_oracle_on_every_variant():
             torch.cuda.synchronize()
             if ran is not None:
                 assert N.lib.bt_preprocess_last_variant() == ran, (shape, variant, layout)
+            elif shape == (7, 7, 5, 4):     # odd width: planar output by aligned groups, interleaved by pixels
+                assert N.lib.bt_preprocess_last_variant() == (5 if layout == "NCHW" else 4)
             assert out.shape[0] == len(idx)
             exp = _oracle(frames[idx], flip, 2.2, kw.get("mean"), kw.get("std"), layout, dtype)
             _assert_matches(out, exp, dtype)

@@ -113,7 +113,7 @@ def main():
         cases += [dict(shape=C2, dtype=torch.float32, variant=v, streams=n) for v in ("bulk",) for n in (1, 2, 4)]
         cases += [dict(shape=C4, dtype=torch.float32, variant="bulk")]
     elif len(sys.argv) > 1 and sys.argv[1] == "table":
-        # host-built table in kernel parameters (default) against the table built by every CTA (bit 19)
+        # the table built by every CTA (default) against a host-built table in kernel parameters (bit 19)
         cases = [dict(shape=sh, dtype=dt, tune=t, streams=n, stats=st) for sh in (C2, (16, 480, 640, 4), C5, C4)
                  for dt in (torch.float32, torch.bfloat16) for st in (False, True) for t in (0, 0x80000)
                  for n in ((1, 4) if sh[0] <= 16 else (1,))] * 2
