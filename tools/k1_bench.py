@@ -119,6 +119,11 @@ def main():
                  for n in ((1, 4) if sh[0] <= 16 else (1,))] * 2
         cases += [dict(shape=C4, dtype=torch.uint8, layout="NHWC", tune=t) for t in (0, 0x80000)]
         cases += [dict(shape=sh, dtype=torch.float32, layout="NHWC", tune=t) for sh in (C2, C4) for t in (0, 0x80000)]
+    elif len(sys.argv) > 1 and sys.argv[1] == "waves":
+        # grids trimmed to whole resident waves (cap = CTAs per SM) at the headline batch and around it
+        cases = [dict(shape=(b, 480, 640, 4), dtype=dt, streams=n, tune=cap << 8, stats=st)
+                 for b in (8, 16) for dt in (torch.float32, torch.bfloat16) for st in (False, True)
+                 for cap in (0, 8, 16, 24, 32) for n in (1, 4)] * 2
     elif len(sys.argv) > 1 and sys.argv[1] == "odd":
         # odd widths: aligned plane groups (auto, k1_window) against one pixel per thread (k1_pixel)
         cases = [dict(shape=sh, dtype=dt, variant=v, streams=n, stats=st)
