@@ -119,6 +119,10 @@ def main():
                  for n in ((1, 4) if sh[0] <= 16 else (1,))] * 2
         cases += [dict(shape=C4, dtype=torch.uint8, layout="NHWC", tune=t) for t in (0, 0x80000)]
         cases += [dict(shape=sh, dtype=torch.float32, layout="NHWC", tune=t) for sh in (C2, C4) for t in (0, 0x80000)]
+    elif len(sys.argv) > 1 and sys.argv[1] == "ncu":
+        # a short run for `ncu --set full`: the headline launch, its statistics variant, C4, and an odd width
+        cases = [dict(shape=C2, dtype=torch.float32, reps=16), dict(shape=C2, dtype=torch.float32, stats=True, reps=16),
+                 dict(shape=C4, dtype=torch.float32, reps=4), dict(shape=(64, 481, 641, 4), dtype=torch.float32, reps=4)]
     elif len(sys.argv) > 1 and sys.argv[1] == "waves":
         # grids trimmed to whole resident waves (cap = CTAs per SM) at the headline batch and around it
         cases = [dict(shape=(b, 480, 640, 4), dtype=dt, streams=n, tune=cap << 8, stats=st)
