@@ -17,6 +17,7 @@ memo still replay here the way they do there (sequentially), because ``__getitem
 Unpickler per open file exactly like file.py:110-112.
 """
 import io
+import os
 import logging
 import mmap
 import pickle
@@ -202,10 +203,68 @@ class FileReader:
 
     @staticmethod
     def read_offsets(fname):
-        """Offsets of the stored messages: the header array cut at its first -1 (file.py:120-132)."""
+        """Offsets of the stored messages: the header array cut at its first -1 (file.py:120-132).
+
+        The header is a pickled int64 array of the recorder's whole capacity -- 800 KB at the default
+        100000 -- however few messages were stored, and the reference unpickles it on every open.  If an
+        index sidecar written by `write_index` sits next to the recording and still matches it (size and
+        modification time), the offsets come from there: a read of 8 bytes per stored message."""
         assert Path(fname).exists(), f"Cannot open {fname} for reading."
+        cached = FileReader._read_index(fname)
+        if cached is not None:
+            return cached
         with io.open(fname, "rb") as f:
             offsets = pickle.Unpickler(f).load()
         unused = np.flatnonzero(offsets == -1)
         count = int(unused[0]) if len(unused) else len(offsets)
         return offsets[:count]
+
+    # ---- index sidecar (SURVEY.md 8f, N1; optional, never required) ------------------------------------
+    _INDEX_MAGIC = b"BTRIDX1\n"
+
+    @staticmethod
+    def index_name(fname):
+        return str(fname) + ".idx"
+
+    @staticmethod
+    def write_index(fname):
+        """Write `<fname>.idx`: magic, the recording's size and mtime_ns, the message count and the int64
+        offsets.  Opening the recording then skips the capacity-sized pickled header.  The recording
+        itself is untouched (it stays readable by the reference); a sidecar that no longer matches its
+        recording is ignored."""
+        offsets = np.ascontiguousarray(FileReader._header_offsets(fname), dtype="<i8")
+        st = os.stat(fname)
+        tmp = FileReader.index_name(fname) + ".tmp%d" % os.getpid()
+        with io.open(tmp, "wb") as f:
+            f.write(FileReader._INDEX_MAGIC)
+            f.write(np.array([st.st_size, st.st_mtime_ns, len(offsets)], dtype="<i8").tobytes())
+            f.write(offsets.tobytes())
+        os.replace(tmp, FileReader.index_name(fname))
+        return FileReader.index_name(fname)
+
+    @staticmethod
+    def _header_offsets(fname):
+        with io.open(fname, "rb") as f:
+            offsets = pickle.Unpickler(f).load()
+        unused = np.flatnonzero(offsets == -1)
+        return offsets[:int(unused[0]) if len(unused) else len(offsets)]
+
+    @staticmethod
+    def _read_index(fname):
+        try:
+            with io.open(FileReader.index_name(fname), "rb") as f:
+                if f.read(8) != FileReader._INDEX_MAGIC:
+                    return None
+                size, mtime_ns, count = np.frombuffer(f.read(24), dtype="<i8")
+                st = os.stat(fname)
+                if size != st.st_size or mtime_ns != st.st_mtime_ns or count < 0:
+                    return None
+                data = f.read(8 * int(count))
+            if len(data) != 8 * int(count):
+                return None
+            offsets = np.frombuffer(data, dtype="<i8").astype(np.int64)
+            if len(offsets) and (offsets[0] < 0 or offsets[-1] >= size or np.any(np.diff(offsets) <= 0)):
+                return None
+            return offsets
+        except (OSError, ValueError):
+            return None

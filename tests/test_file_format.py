@@ -130,3 +130,44 @@ def test_concurrent_first_use_of_the_mapping(golden_dir):
         [t.join() for t in ts]
         assert not errs and len({x[0] for x in out}) == 1 and len({x[1] for x in out}) == 1
         r.close()
+
+
+def test_index_sidecar_skips_the_capacity_sized_header(tmp_path):
+    """N1's optional `.btr.idx`: the offsets without unpickling the 800 KB header of a default-capacity
+    recording; ignored as soon as it no longer matches the recording; the recording itself unchanged."""
+    import os
+    import pickle
+    import time
+    from blendtorch import btt
+    name = str(tmp_path / "rec_00.btr")
+    msgs = [pickle.dumps({"btid": 0, "frameid": i, "image": np.full((4, 6, 4), i, np.uint8)}, protocol=3) for i in range(9)]
+    with btt.FileRecorder(name) as rec:                         # default capacity: 100000 offsets in the header
+        for m in msgs:
+            rec.save(m, is_pickled=True)
+    before = open(name, "rb").read()
+    plain = btt.FileReader.read_offsets(name)
+    idx = btt.FileReader.write_index(name)
+    assert os.path.getsize(idx) == 8 + 24 + 8 * 9 and open(name, "rb").read() == before
+    np.testing.assert_array_equal(btt.FileReader._read_index(name), plain)
+    r = btt.FileReader(name)
+    assert len(r) == 9 and r[4]["frameid"] == 4 and bytes(r.raw(8)) == msgs[8]
+    r.close()
+    t0 = time.perf_counter()
+    for _ in range(20):
+        btt.FileReader.read_offsets(name)
+    with_idx = time.perf_counter() - t0
+    os.rename(idx, idx + ".off")
+    t0 = time.perf_counter()
+    for _ in range(20):
+        btt.FileReader.read_offsets(name)
+    without = time.perf_counter() - t0
+    assert with_idx < without                                   # 104 bytes against an 800 KB pickle
+    os.rename(idx + ".off", idx)
+    # a recording that changed after the sidecar was written: the sidecar is ignored, not trusted
+    with btt.FileRecorder(name, max_messages=16) as rec:
+        for m in msgs[:3]:
+            rec.save(m, is_pickled=True)
+    assert btt.FileReader._read_index(name) is None and len(btt.FileReader(name)) == 3
+    # garbage sidecars are ignored too
+    open(idx, "wb").write(b"BTRIDX1\n" + b"\xff" * 40)
+    assert btt.FileReader._read_index(name) is None and len(btt.FileReader.read_offsets(name)) == 3
