@@ -506,3 +506,35 @@ def test_depth_field_is_flipped_with_fliprows(tmp_path):
         dl.close()
     with pytest.raises(TypeError, match="uint8"):
         list(btt.DeviceLoader(ds, batch_size=4, device=DEV, preprocess=btt.Preprocess(key="depth")))
+
+
+def _slow_publisher(addr, count, rate, h, w):
+    S.run_publisher(addr, 0, 2, h, w, 4, count=count, pool=count, protocol=3, lingerms=10000, rate=rate)
+
+
+@pytest.mark.parametrize("drop_last", [False, True])
+def test_groups_of_batches_hand_out_what_is_complete_when_the_stream_pauses(drop_last):
+    """group=4 stages 4 batches per pinned slot.  A slow publisher must not make the consumer wait for a
+    whole group: when the stream pauses on a batch boundary the complete batches are handed out; the
+    batches are the same as with group=1, in order, and the last, short one follows drop_last."""
+    H, W, count = 24, 32, 10
+    out = {}
+    for group in (1, 4):
+        addr = "tcp://127.0.0.1:%d" % _free_port()
+        ctx = mp.get_context("spawn")
+        p = ctx.Process(target=_slow_publisher, args=(addr, count, 25.0, H, W), daemon=True)
+        p.start()
+        try:
+            ds = btt.RemoteIterableDataset([addr], max_items=count, timeoutms=20000)
+            dl = btt.DeviceLoader(ds, batch_size=4, device=DEV, group=group, drop_last=drop_last,
+                                  preprocess=btt.Preprocess(flip=True, gamma=2.2, mean=127.5, std=127.5, stats=True))
+            got = [(b["frameid"].tolist(), b["image"].cpu(), b["image_stats"].cpu()) for b in dl]
+            dl.close()
+            out[group] = got
+        finally:
+            p.join(timeout=15)
+    sizes = [len(f) for f, _, _ in out[4]]
+    assert sizes == ([4, 4] if drop_last else [4, 4, 2])
+    assert [f for f, _, _ in out[4]] == [f for f, _, _ in out[1]] == ([[0, 1, 2, 3], [4, 5, 6, 7]] + ([] if drop_last else [[8, 9]]))
+    for (_, img1, st1), (_, img4, st4) in zip(out[1], out[4]):
+        assert torch.equal(img1, img4) and torch.equal(st1, st4)       # per-batch statistics stay per batch
