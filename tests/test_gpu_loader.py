@@ -522,7 +522,7 @@ def test_groups_of_batches_hand_out_what_is_complete_when_the_stream_pauses(drop
     for group in (1, 4):
         addr = "tcp://127.0.0.1:%d" % _free_port()
         ctx = mp.get_context("spawn")
-        p = ctx.Process(target=_slow_publisher, args=(addr, count, 25.0, H, W), daemon=True)
+        p = ctx.Process(target=_slow_publisher, args=(addr, count, 6.0, H, W), daemon=True)   # 167 ms apart: every wait times out once
         p.start()
         try:
             ds = btt.RemoteIterableDataset([addr], max_items=count, timeoutms=20000)
