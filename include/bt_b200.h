@@ -300,8 +300,10 @@ int bt_shm_release(bt_shm* s, int ticket);
  * served round-robin skipping those that cannot take more (PUSH load balancing), and the sender
  * blocks when no peer can take a message (SNDHWM back-pressure, publisher.py:24; the queue here is
  * the kernel socket buffer plus one message in progress per peer).
- * One bt_push holds any number of bound endpoints ("publishers"); an endpoint must be driven by one
- * thread at a time.
+ * One bt_push holds any number of bound endpoints ("publishers").  Threading: bind every endpoint before
+ * any thread sends; after that an endpoint belongs to one thread at a time -- bt_push_send, bt_push_run
+ * over a range that contains it, and bt_push_peers all touch its connection list -- while different
+ * endpoints may be driven by different threads concurrently.
  * ------------------------------------------------------------------------------------------ */
 typedef struct bt_push bt_push;
 

@@ -132,7 +132,8 @@ class NativePublisher:
         self._sent = []
 
     def peers(self, endpoint=0):
-        """Consumers connected to `endpoint` right now."""
+        """Consumers connected to `endpoint` right now (not while `start`'s threads are running: an
+        endpoint's connection list belongs to one thread at a time)."""
         return self._N.check(self._N.lib.bt_push_peers(self.handle, endpoint))
 
     def publish_raw(self, data, endpoint=0, timeoutms=-1):
