@@ -645,12 +645,15 @@ def host_probes(ctx):
     return out
 
 
-def socket_probe(ctx, transport, receivers, senders, seconds=1.0):
-    """Images/s of the socket path alone for C2 messages: native publishers -> `receivers` direct
-    receivers filling an unpinned ring (scan + the one copy), no GPU, no Python per message."""
+def socket_probe(ctx, transport, receivers, senders, seconds=1.0, cfg=None):
+    """Images/s of the socket path alone (C2 messages unless `cfg` says otherwise): native publishers ->
+    `receivers` direct receivers filling an unpinned ring (scan + the one copy), no GPU, no Python per
+    message."""
     from blendtorch.btt.rx import DirectReceiver
     from blendtorch.btt.staging import Ring, Schema
-    addrs, proc = spawn_native_publisher(PUBLISHERS, transport, threads=senders, tag="sp%d" % ctx["rank"], cpus=ctx["cpus"])
+    cfg = cfg or {"config": CONFIG, "h": H, "w": W, "publishers": PUBLISHERS}
+    addrs, proc = spawn_native_publisher(cfg["publishers"], transport, threads=min(senders, cfg["publishers"]),
+                                         tag="sp%d" % ctx["rank"], cpus=ctx["cpus"], config=cfg["config"], h=cfg["h"], w=cfg["w"])
     counts = [0] * receivers
     try:
         def run(r):
@@ -834,7 +837,19 @@ def ours(args):
                          "stream, %d native publishers over %s, %d receivers" % (PUBLISHERS, args.transport, receivers))
             # C5: 128x128 RGBA, batch 1024, 16 publishers
             c5 = {"name": "C5", "config": 5, "h": 128, "w": 128, "batch": 1024, "publishers": 16}
+            # 64 KiB messages cost per message, not per byte: the split that suits C2 need not suit them.
+            # Try the neighbours of the C2 rule on the socket path alone and keep the best (every rank
+            # measures at once; all ranks take the same choice).
             s5, rcv5, _ = split_threads(len(cpus), s_rate or 1.0, r_rate or 1.0, 16)
+            budget = s5 + rcv5
+            best = None
+            for cand in sorted({(s5, rcv5), (max(1, s5 - 1), min(8, budget - max(1, s5 - 1))), (min(16, s5 + 1), max(1, budget - min(16, s5 + 1)))}):
+                barrier()
+                rate = min(gather(socket_probe(ctx, args.transport, cand[1], cand[0], 0.8, cfg=c5)))
+                if best is None or rate > best[0] * 1.03:
+                    best = (rate, cand)
+            barrier()
+            s5, rcv5 = best[1]
             r5 = stream_leg(ctx, c5, args.transport, rcv5, s5, min_seconds=1.5)
             barrier()
             raw["C5"] = (r5, kernel_times(torch, btt, dev, 128, 128, 1024),

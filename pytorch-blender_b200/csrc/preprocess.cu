@@ -928,6 +928,10 @@ int launch_typed(const bt_preprocess_params* p, K1Args& a, int variant, cudaStre
       LAUNCH_PLANAR(4, 8, 2);
     }
     if (a.W % 4 == 0) {
+      if (STATS && sizeof(T) == 4) {   // A/B: fewer units in flight per thread, fewer registers, more CTAs per SM
+        if (tune_unroll == 1) LAUNCH_PLANAR(4, 4, 1);
+        if (tune_unroll == 2) LAUNCH_PLANAR(4, 4, 2);
+      }
       if (!STATS && sizeof(T) == 4) {
         if (tune_unroll == 1) LAUNCH_PLANAR(4, 4, 1);
         if (tune_unroll == 2) LAUNCH_PLANAR(4, 4, 2);

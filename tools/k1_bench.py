@@ -123,6 +123,22 @@ def main():
         # a short run for `ncu --set full`: the headline launch, its statistics variant, C4, and an odd width
         cases = [dict(shape=C2, dtype=torch.float32, reps=16), dict(shape=C2, dtype=torch.float32, stats=True, reps=16),
                  dict(shape=C4, dtype=torch.float32, reps=4), dict(shape=(64, 481, 641, 4), dtype=torch.float32, reps=4)]
+    elif len(sys.argv) > 1 and sys.argv[1] == "statsunroll":
+        # statistics variant: units in flight per thread (registers vs occupancy) x grid cap
+        cases = [dict(shape=sh, dtype=torch.float32, stats=True, streams=n, tune=u | (cap << 8))
+                 for sh in (C2, (16, 480, 640, 4), C5, C4) for u in (0, 1, 2) for cap in (0, 4, 8, 16)
+                 for n in ((1, 4) if sh[0] <= 16 else (1,))]
+    elif len(sys.argv) > 1 and sys.argv[1] == "single":
+        # one launch alone at the headline batch: units per thread x whole-wave grids, and the bulk variant
+        cases = [dict(shape=C2, dtype=torch.float32, streams=n, tune=t) for t in (0, 0x2, 0x802, 0x402, 0x808, 0x408, 0x801, 0x1001)
+                 for n in (1, 4)] * 2
+        cases += [dict(shape=C2, dtype=torch.float32, streams=n, variant="bulk", tune=t) for t in (0, 0x800, 0x600) for n in (1, 4)]
+    elif len(sys.argv) > 1 and sys.argv[1] == "bulksmall":
+        # where the bulk variant (8 CTAs per SM) beats the register kernel: small batches, alone and overlapped
+        cases = [dict(shape=sh, dtype=dt, streams=n, variant=v, tune=t)
+                 for sh in ((4, 480, 640, 4), (8, 480, 640, 4), (12, 480, 640, 4), (16, 480, 640, 4), (24, 480, 640, 4),
+                            (32, 480, 640, 4), (4, 1024, 1024, 4), (8, 1024, 1024, 4), (2, 1080, 1920, 4), (32, 256, 256, 4))
+                 for dt in (torch.float32, torch.bfloat16) for v, t in (("auto", 0), ("bulk", 0x800)) for n in (1, 4)] * 2
     elif len(sys.argv) > 1 and sys.argv[1] == "waves":
         # grids trimmed to whole resident waves (cap = CTAs per SM) at the headline batch and around it
         cases = [dict(shape=(b, 480, 640, 4), dtype=dt, streams=n, tune=cap << 8, stats=st)
