@@ -62,11 +62,22 @@ def _use_product():
 
 
 def free_port():
-    s = socket.socket()
-    s.bind(("127.0.0.1", 0))
-    p = s.getsockname()[1]
-    s.close()
-    return p
+    """A port nobody listens on, taken from below the kernel's ephemeral range (32768-60999): the address
+    is handed to a process that binds it a moment later, and meanwhile no outgoing connection of ours
+    can be given the same number as its source port."""
+    import random
+    import socket
+    for _ in range(200):
+        port = random.randint(20000, 32000)
+        s = socket.socket()
+        try:
+            s.bind(("127.0.0.1", port))
+        except OSError:
+            continue
+        finally:
+            s.close()
+        return port
+    raise RuntimeError("no free port found")
 
 
 def spawn_publishers(module, n, transport="tcp", tag="p", extra=()):

@@ -18,11 +18,22 @@ DEV = "cuda:0"
 
 
 def _free_port():
-    s = socket.socket()
-    s.bind(("127.0.0.1", 0))
-    p = s.getsockname()[1]
-    s.close()
-    return p
+    """A port nobody listens on, taken from below the kernel's ephemeral range (32768-60999): the address
+    is handed to a process that binds it a moment later, and meanwhile no outgoing connection of ours
+    can be given the same number as its source port."""
+    import random
+    import socket
+    for _ in range(200):
+        port = random.randint(20000, 32000)
+        s = socket.socket()
+        try:
+            s.bind(("127.0.0.1", port))
+        except OSError:
+            continue
+        finally:
+            s.close()
+        return port
+    raise RuntimeError("no free port found")
 
 
 def test_replay_equals_reference_collate(golden_dir):

@@ -30,12 +30,22 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _free_port():
+    """A port nobody listens on, taken from below the kernel's ephemeral range (32768-60999): the address
+    is handed to a process that binds it a moment later, and meanwhile no outgoing connection of ours
+    can be given the same number as its source port."""
+    import random
     import socket
-    s = socket.socket()
-    s.bind(("127.0.0.1", 0))
-    p = s.getsockname()[1]
-    s.close()
-    return p
+    for _ in range(200):
+        port = random.randint(20000, 32000)
+        s = socket.socket()
+        try:
+            s.bind(("127.0.0.1", port))
+        except OSError:
+            continue
+        finally:
+            s.close()
+        return port
+    raise RuntimeError("no free port found")
 
 
 def _addresses(n, transport, tag):
@@ -59,6 +69,8 @@ def _spawn(addrs, config, h, w, protocol, count, native=False, extra=()):
 
 def _stop(procs):
     for p in procs:
+        if p.poll() not in (None, 0):      # a publisher that died on its own: say so next to whatever failed
+            print("publisher %s exited with %s before the test ended" % (p.args[-6:], p.returncode))
         p.terminate()
     for p in procs:
         try:
