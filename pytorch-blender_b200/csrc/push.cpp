@@ -514,8 +514,10 @@ int bt_push_run(bt_push* p, const bt_push_job* job) {
           const uint64_t before_cur = q.cur, before_off = q.off;
           const int rc = pump(q);
           if (rc < 0) {
-            // Connection lost with a message in progress: like libzmq, that message is gone with the
-            // pipe; a shared-memory slot it announced comes back at once.
+            // Connection lost.  A message of which nothing had been written yet is simply taken back (it
+            // goes to the next peer); one that was under way is gone with the pipe, like in libzmq.  A
+            // shared-memory slot it announced comes back at once either way.
+            if (q.cur == 0 && q.off == 0 && before_cur == 0 && before_off == 0 && e.started > 0) --e.started;
             if (job->seg && q.ticket >= 0) bt_shm_release(job->seg[ei], q.ticket);
             q.ticket = -1;
             close_peer(q);
