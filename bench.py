@@ -691,7 +691,7 @@ def socket_probe(ctx, transport, receivers, senders, seconds=1.0, cfg=None):
     return sum(counts) / seconds
 
 
-def split_threads(cores, sender_rate, receiver_rate, max_senders, max_receivers=8):
+def split_threads(cores, sender_rate, receiver_rate, max_senders, max_receivers=10):
     """Sender and receiver thread counts for one rank from the measured per-thread rates: the split of
     (cores - 1) threads (one core stays with the consumer / interpreter) that maximises
     min(senders * sender_rate, receivers * receiver_rate)."""
@@ -830,7 +830,7 @@ def ours(args):
             S.write_recordings(tmp + "/c3", 3, 2, 64, 1080, 1920, pool=8)
             cam = btt.Camera.from_lens((1080, 1920), lens=35.0, distance=0.0, device=dev)
             pj = btt.Projection("corners", camera=cam, xy_key="corners_xy", bbox_key="boxes", corners_per_object=8)
-            r3 = replay_leg(ctx, c3, tmp + "/c3", project=pj, depth_flip=True, threads=max(1, min(8, len(cpus) - 3)),
+            r3 = replay_leg(ctx, c3, tmp + "/c3", project=pj, depth_flip=True, threads=max(1, min(12, len(cpus) - 3)),
                             min_seconds=1.5)
             barrier()
             r3h = replay_leg(ctx, c3, tmp + "/c3", cache="host", project=pj, depth_flip=True, min_seconds=1.5)
