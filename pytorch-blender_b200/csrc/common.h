@@ -119,6 +119,14 @@ uint64_t stream_big_len();
 int stream_big_target(const bt_schema* schema, int* column);
 int stream_fields(const uint8_t* buf, std::vector<bt_field>& out);
 
+// Copy into staging memory that the CPU will not read again (a pinned slot or a shared-memory slot that
+// only a DMA engine reads next): non-temporal stores, so that the destination lines are not first read
+// into the cache for ownership -- a plain memcpy moves three bytes over the memory bus per byte copied
+// (read source, read destination, write destination), this moves two.  Every path that stages by CPU copy
+// is bound by the host's memory bandwidth, so that is a third off its cost.  Falls back to
+// memcpy for small sizes, CPUs without AVX2, and BT_STREAM_COPY=0 (the A/B switch).
+void stream_copy(void* dst, const void* src, size_t n);
+
 // Process-wide registry of attached segments (shm.cu).
 int shm_attach_cached(const char* name, size_t name_len, int device, bt_shm** out);
 

@@ -491,7 +491,7 @@ int bt_push_run(bt_push* p, const bt_push_job* job) {
                   return bt::fail(BT_E_TOO_LARGE, "payload of %llu bytes does not fit a shared-memory slot",
                                   (unsigned long long)job->payload_len[m]);
                 }
-                memcpy(bt_shm_slot_ptr(seg, ticket), job->payload[m], job->payload_len[m]);
+                bt::stream_copy(bt_shm_slot_ptr(seg, ticket), job->payload[m], job->payload_len[m]);
               }
               q.small.assign(job->pool[m], job->pool[m] + job->pool_len[m]);
               if ((uint64_t)job->tmpl_ticket_off[m] + 4 > q.small.size()) {

@@ -188,7 +188,7 @@ int bt_ring_spill(bt_ring* r, int slot, const bt_schema* s) {
   uint8_t* base = r->base + r->slot_bytes * (uint64_t)slot;
   for (const bt::PendingRef& p : r->pending[slot]) {
     const bt_column& c = s->cols[p.column];
-    memcpy(base + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot), p.nbytes);
+    bt::stream_copy(base + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot), p.nbytes);
   }
   return release_refs(r->pending[slot]);   // the release doubles as the "still ours after the copy" check
 }
@@ -225,7 +225,7 @@ int bt_ring_submit_batch(bt_ring* r, int slot, const bt_schema* s, int n_items, 
     if (by_ref[ci] > 0 && rc == BT_OK) {                         // mixed: bring the referenced items in first
       for (const bt::PendingRef& p : pend)
         if (p.column == (int)ci)
-          memcpy(host + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot), p.nbytes);
+          bt::stream_copy(host + c.slot_off + c.item_bytes * (uint64_t)p.item, bt_shm_slot_ptr(p.seg, p.shm_slot), p.nbytes);
     }
     const uint64_t nbytes = c.item_bytes * (uint64_t)n_items;
     if (nbytes) copy(dev + c.slot_off, host + c.slot_off, nbytes);

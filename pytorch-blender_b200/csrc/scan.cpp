@@ -8,6 +8,10 @@
 // (protocol 5, in-band) and `scalar` (numpy scalars).  Anything outside the whitelist returns
 // BT_E_UNSUPPORTED and the Python layer falls back to pickle.loads, which is what the reference
 // does for every message.  No callable named by the pickle is ever invoked.
+#if defined(__x86_64__)
+#include <immintrin.h>
+#endif
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <thread>
@@ -635,10 +639,52 @@ uint64_t field_bytes(const bt_field& f) {
 }
 
 namespace {
+#if defined(__x86_64__)
+__attribute__((target("avx2"))) void stream_copy_avx2(uint8_t* d, const uint8_t* s, size_t n) {
+  size_t head = (32 - (reinterpret_cast<uintptr_t>(d) & 31)) & 31;   // stores must be 32-byte aligned
+  if (head > n) head = n;
+  memcpy(d, s, head);
+  d += head; s += head; n -= head;
+  while (n >= 128) {
+    const __m256i a = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(s));
+    const __m256i b = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(s + 32));
+    const __m256i c = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(s + 64));
+    const __m256i e = _mm256_loadu_si256(reinterpret_cast<const __m256i*>(s + 96));
+    _mm256_stream_si256(reinterpret_cast<__m256i*>(d), a);
+    _mm256_stream_si256(reinterpret_cast<__m256i*>(d + 32), b);
+    _mm256_stream_si256(reinterpret_cast<__m256i*>(d + 64), c);
+    _mm256_stream_si256(reinterpret_cast<__m256i*>(d + 96), e);
+    d += 128; s += 128; n -= 128;
+  }
+  while (n >= 32) {
+    _mm256_stream_si256(reinterpret_cast<__m256i*>(d), _mm256_loadu_si256(reinterpret_cast<const __m256i*>(s)));
+    d += 32; s += 32; n -= 32;
+  }
+  memcpy(d, s, n);
+  _mm_sfence();   // the data is globally visible before whatever announces it (an event, a ticket, a doorbell)
+}
+#endif
+}  // namespace
+
+void stream_copy(void* dst, const void* src, size_t n) {   // (this file is inside namespace bt here)
+#if defined(__x86_64__)
+  static const bool on = [] {
+    const char* e = getenv("BT_STREAM_COPY");
+    return !(e && e[0] == '0') && __builtin_cpu_supports("avx2");
+  }();
+  if (on && n >= 4096) {
+    stream_copy_avx2(static_cast<uint8_t*>(dst), static_cast<const uint8_t*>(src), n);
+    return;
+  }
+#endif
+  memcpy(dst, src, n);
+}
+
+namespace {
 constexpr uint64_t kChunk = 256 * 1024;
 void copy_or_defer(uint8_t* dst, const uint8_t* src, uint64_t n, std::vector<CopyTask>* tasks) {
   if (!tasks || n < 64 * 1024) {
-    memcpy(dst, src, n);
+    stream_copy(dst, src, n);
     return;
   }
   for (uint64_t off = 0; off < n; off += kChunk)
@@ -759,7 +805,7 @@ int place_fields(const bt_schema* s, uint8_t* base, int item, const uint8_t* msg
         if (refs) {
           refs->push_back(PendingRef{seg, ticket, (int)ci, item, c.item_bytes});
         } else {
-          memcpy(dst, bt_shm_slot_ptr(seg, ticket), c.item_bytes);
+          stream_copy(dst, bt_shm_slot_ptr(seg, ticket), c.item_bytes);
           rc = bt_shm_check(seg, ticket);  // and it stayed ours while we copied
           if (rc != BT_OK) return rc;
           bt_shm_release(seg, ticket);
@@ -894,7 +940,7 @@ int bt_schema_ingest_many(const bt_schema* s, void* slot_base, int first_item, i
   }
   if (!tasks.empty()) {
     const std::vector<CopyTask>& t = tasks;
-    WorkPool::get().run(nthreads, t.size(), [&t](size_t k) { memcpy(t[k].dst, t[k].src, t[k].n); });
+    WorkPool::get().run(nthreads, t.size(), [&t](size_t k) { stream_copy(t[k].dst, t[k].src, t[k].n); });
   }
   return BT_OK;
 }
