@@ -13,6 +13,14 @@
  * There is no CPU implementation of the kernels behind this header: if no CUDA
  * device is usable the launch functions fail with BT_E_CUDA.
  */
+/*
+ * Environment switches read by the library (all optional):
+ *   BT_MAX_MESSAGE_BYTES  largest frame / message the direct receiver accepts (default 4 GiB)
+ *   BT_PULL_RCVBUF, BT_PUSH_SNDBUF   socket buffer sizes in bytes (default 1 MiB each)
+ *   BT_SHM_LEASE_MS       lease of shared-memory slots at segment creation (default 30000, 0 = never taken back)
+ *   BT_STREAM_COPY=0      staging copies with plain memcpy instead of non-temporal stores (A/B switch)
+ *   BT_RX_READAHEAD=0     direct receiver without its read-ahead buffer (A/B switch), BT_RX_STATS=1 prints its counters
+ */
 #ifndef BT_B200_H
 #define BT_B200_H
 
