@@ -691,6 +691,19 @@ def socket_probe(ctx, transport, receivers, senders, seconds=1.0, cfg=None):
     return sum(counts) / seconds
 
 
+def stream_threads(cores, endpoints):
+    """(sender threads, receiver threads) of one rank for the large-frame stream legs.
+
+    One sender thread per publisher endpoint, always: a sender sleeps in poll() while its consumers'
+    sockets are full, so it costs little beyond its copies, whereas a thread that serves several
+    endpoints keeps retrying the full sockets of one while another still takes data -- and in the
+    sweeps behind this rule (profiles/r2_e2e_sweep_native.jsonl, r2_sender_threads.jsonl) exactly the
+    unbalanced split of 4 threads over 5 endpoints collapsed now and then (5 k instead of 24 k images/s),
+    while 5 threads on 4 cores carried 43 % more than 1.  Receivers: two thirds of the rank's cores but
+    one (16 cores: 10 -> 26.0 k images/s against 24.0 k with 8; 12: 7; 8: 4; 4: 2), at most 10."""
+    return endpoints, max(1, min(10, (cores - 1) * 2 // 3))
+
+
 def split_threads(cores, sender_rate, receiver_rate, max_senders, max_receivers=10):
     """Sender and receiver thread counts for one rank from the measured per-thread rates: the split of
     (cores - 1) threads (one core stays with the consumer / interpreter) that maximises
@@ -777,8 +790,8 @@ def ours(args):
     if args.senders > 0 and args.receivers > 0:
         senders, receivers = args.senders, args.receivers
     else:
-        # per-thread rates of the socket path on this rank's cores: 1 sender feeding 3 receivers is
-        # sender-bound, 3 senders feeding 1 receiver is receiver-bound (C2 messages)
+        # per-thread rates of the socket path on this rank's cores (reported, and the basis of the C5 split):
+        # 1 sender feeding 3 receivers is sender-bound, 3 senders feeding 1 receiver is receiver-bound
         spare = max(1, len(cpus) - 2)
         barrier()
         s_rate = socket_probe(ctx, args.transport, min(3, spare), 1, 0.8)
@@ -786,7 +799,7 @@ def ours(args):
         r_rate = socket_probe(ctx, args.transport, 1, min(3, PUBLISHERS, spare), 0.8)
         barrier()
         s_rate, r_rate = max(1.0, min(gather(s_rate))), max(1.0, min(gather(r_rate)))
-        senders, receivers, _ = split_threads(len(cpus), s_rate, r_rate, PUBLISHERS)
+        senders, receivers = stream_threads(len(cpus), PUBLISHERS)
         if args.senders > 0:
             senders = args.senders
         if args.receivers > 0:
@@ -992,7 +1005,7 @@ def _report(args, ctx, gather, dist, dleg, value, achieved, sec_per_launch, algo
                                  "already stand in page-locked memory (in-place shared memory, cache='host'): those scale "
                                  "with the GPUs' concurrent PCIe rate instead"},
                      "sender_images_per_s_per_thread": s_rate, "receiver_images_per_s_per_thread": r_rate,
-                     "thread_split": "senders %d, receivers %d per rank (from the per-thread rates)" % (senders, receivers)},
+                     "thread_split": "senders %d (one per endpoint), receivers %d per rank" % (senders, receivers)},
             "gpu_launches": dleg["overlapped"]["launches_timed"],
             # e2e batches carry statistics (the step's result that is read back): K1 + the fold kernel of its rows
             "gpu_launches_e2e": 2 * tcp["batches"],
