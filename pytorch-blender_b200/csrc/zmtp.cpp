@@ -285,6 +285,12 @@ int handshake(int fd) {
   rc = read_exact(fd, body.data(), size, 2000);
   if (rc != BT_OK) return rc;
   if (body[0] != 5 || memcmp(&body[1], "READY", 5) != 0) return bt::fail(BT_E_UNSUPPORTED, "peer refused the connection");
+  // a PULL socket takes messages from PUSH peers only (ZMTP 3.0 socket type compatibility)
+  static const char want[] = "\x0bSocket-Type\0\0\0\x04PUSH";
+  bool push = false;
+  for (uint64_t i = 6; i + sizeof want - 1 <= size; ++i)
+    if (memcmp(body.data() + i, want, sizeof want - 1) == 0) push = true;
+  if (!push) return bt::fail(BT_E_UNSUPPORTED, "peer is not a PUSH socket");
   return BT_OK;
 }
 
@@ -321,10 +327,36 @@ void start_connect(Peer& p) {
   }
 }
 
+// A TCP socket that keeps trying a local port on which nobody listens yet can end up connected to
+// *itself*: when the kernel happens to pick the destination port as the source port, the connection
+// opens simultaneously with itself.  It would then pass its own greeting back to us, look like a
+// publisher that never sends anything, and -- worse -- occupy the very port the publisher is about to
+// bind ("Address already in use" in the publisher).  Consumers started before their producers, as
+// blendtorch's launch order allows, retry often enough to meet this.
+bool connected_to_itself(int fd) {
+  sockaddr_storage a, b;
+  socklen_t la = sizeof a, lb = sizeof b;
+  if (getsockname(fd, reinterpret_cast<sockaddr*>(&a), &la) != 0 || getpeername(fd, reinterpret_cast<sockaddr*>(&b), &lb) != 0)
+    return false;
+  if (a.ss_family != b.ss_family) return false;
+  if (a.ss_family == AF_INET) {
+    const sockaddr_in* x = reinterpret_cast<const sockaddr_in*>(&a);
+    const sockaddr_in* y = reinterpret_cast<const sockaddr_in*>(&b);
+    return x->sin_port == y->sin_port && x->sin_addr.s_addr == y->sin_addr.s_addr;
+  }
+  if (a.ss_family == AF_INET6) {
+    const sockaddr_in6* x = reinterpret_cast<const sockaddr_in6*>(&a);
+    const sockaddr_in6* y = reinterpret_cast<const sockaddr_in6*>(&b);
+    return x->sin6_port == y->sin6_port && memcmp(&x->sin6_addr, &y->sin6_addr, sizeof x->sin6_addr) == 0;
+  }
+  return false;
+}
+
 void finish_connect(Peer& p) {
   int err = 0;
   socklen_t len = sizeof err;
-  if (getsockopt(p.fd, SOL_SOCKET, SO_ERROR, &err, &len) != 0 || err != 0 || handshake(p.fd) != BT_OK) {
+  if (getsockopt(p.fd, SOL_SOCKET, SO_ERROR, &err, &len) != 0 || err != 0 || connected_to_itself(p.fd) ||
+      handshake(p.fd) != BT_OK) {
     close_peer(p);
     return;
   }
