@@ -30,13 +30,22 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _free_port():
-    """A port nobody listens on, taken from below the kernel's ephemeral range (32768-60999): the address
-    is handed to a process that binds it a moment later, and meanwhile no outgoing connection of ours
-    can be given the same number as its source port."""
+    """A port nobody listens on, taken from outside the kernel's ephemeral range
+    (/proc/sys/net/ipv4/ip_local_port_range): the address is handed to a process that binds it a moment
+    later, and meanwhile no outgoing connection of ours can be given the same number as its source port
+    (least of all a consumer's retry that connects to itself)."""
     import random
     import socket
-    for _ in range(200):
-        port = random.randint(20000, 32000)
+    lo, hi = 32768, 60999
+    try:
+        with open("/proc/sys/net/ipv4/ip_local_port_range") as f:
+            lo, hi = (int(x) for x in f.read().split()[:2])
+    except (OSError, ValueError):
+        pass
+    spans = [(a, b) for a, b in ((10000, min(lo, 65536) - 1), (hi + 1, 65535)) if b - a >= 500] or [(20000, 32000)]
+    for _ in range(400):
+        a, b = random.choice(spans)
+        port = random.randint(a, b)
         s = socket.socket()
         try:
             s.bind(("127.0.0.1", port))
