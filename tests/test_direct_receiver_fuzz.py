@@ -160,3 +160,47 @@ def test_hostile_peer_never_wedges_the_receiver():
     assert tail == [1000, 1001, 1002, 1003, 1004], (tail, fallbacks)
     # and the good first message of (nearly) every hostile connection did too
     assert len([f for f in seen if f < n_bad]) >= n_bad - 2
+
+
+def test_peers_that_are_not_push_sockets_are_refused_and_a_socket_connected_to_itself_is_dropped():
+    """A PULL endpoint takes messages from PUSH peers only.  This matters beyond protocol hygiene: a consumer
+    that keeps retrying a local port nobody listens on yet can get connected to *itself* (the kernel picks
+    the destination port as the source port); it then reads back its own greeting and its own READY -- a
+    PULL socket -- and would sit on the port its publisher is about to bind.  The endpoint refuses a peer
+    whose Socket-Type is not PUSH (and compares getsockname with getpeername before it even starts)."""
+    good = pickle.dumps(_msg(1), protocol=3)
+
+    class _PullPeer(_Peer):
+        def run(self):
+            c, _ = self.srv.accept()
+            c.settimeout(5)
+            try:
+                c.sendall(_greeting())
+                got = b""
+                while len(got) < 64:
+                    got += c.recv(64 - len(got))
+                body = b"\x05READY" + b"\x0bSocket-Type" + struct.pack(">I", 4) + b"PULL"    # what a mirror would say
+                c.sendall(bytes([0x04, len(body)]) + body)
+                c.recv(64)
+                c.sendall(_frame(good))
+                self.closed_by_endpoint = c.recv(1) == b""        # the endpoint hangs up instead of reading on
+            except OSError:
+                self.closed_by_endpoint = True
+            c.close()
+            self.srv.close()
+
+    peer = _PullPeer([])
+    peer.start()
+    rx = DirectReceiver([peer.addr])
+    assert not rx.recv(1500)                                      # nothing is ever delivered from that peer
+    peer.join(5)
+    assert peer.closed_by_endpoint
+    rx.close()
+    # the mirror itself: a socket connected to its own port (bind, then connect to the bound address)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    s.connect(s.getsockname())
+    assert s.getsockname() == s.getpeername()                     # what finish_connect tests for
+    s.sendall(_greeting())
+    assert s.recv(64) == _greeting()                              # it reads back what it wrote: a valid greeting
+    s.close()
