@@ -409,6 +409,7 @@ int bt_push_send(bt_push* p, int endpoint, const uint8_t* const* parts, const ui
       for (size_t k = 0; k < n; ++k) {
         PushPeer& q = e.peers[(e.rr + k) % n];
         if (q.fd < 0) continue;
+        if (!peer_alive(q)) { close_peer(q); continue; }   // hung up while idle: not a consumer any more
         for (int i = 0; i < nparts; ++i) set_frame(q.frames[i], parts[i], lens[i], i + 1 < nparts);
         q.nframes = nparts;
         q.cur = 0;
@@ -477,6 +478,9 @@ int bt_push_run(bt_push* p, const bt_push_job* job) {
           if (q.fd < 0) continue;
           if (q.nframes == 0) {
             if (!(job->messages < 0 || e.started < job->messages)) continue;
+            // a consumer that has hung up gets no new message (its FIN is waiting to be read: one
+            // non-blocking recv); what was already on its way when it left is lost with it, as in libzmq
+            if (!peer_alive(q)) { close_peer(q); progress = true; continue; }
             size_t m = (size_t)ei * job->pool_n + (size_t)(e.started % job->pool_n);
             if (job->seg) {
               bt_shm* seg = job->seg[ei];

@@ -236,3 +236,54 @@ def test_command_line_native_publisher_feeds_the_reference_style_dataset(tmp_pat
         assert proc.wait(10) == 0
     finally:
         proc.kill()
+
+
+def test_raw_parts_from_the_native_publisher_land_in_the_direct_receivers_columns():
+    """Library to library over the raw-parts wire: `publish_parts` frames (pickled header + array frames)
+    are received straight into the schema's columns by bt_pull_fill; values equal what was published."""
+    rng = np.random.default_rng(5)
+    B = 4
+    items = [{"btid": 7, "image": rng.integers(0, 256, (90, 120, 4), dtype=np.uint8), "frameid": i,
+              "depth": rng.random((90, 120), dtype=np.float32)} for i in range(2 * B)]
+    with btt.NativePublisher("ipc:///tmp/bt_np_raw_%d" % os.getpid()) as pub:
+        rx = DirectReceiver(pub.addresses)
+        sender = threading.Thread(target=lambda: [pub.publish_parts(wire.pack(it), timeoutms=10000) for it in items])
+        sender.start()
+        assert rx.recv(5000)
+        sizes = rx.pending_parts()
+        assert len(sizes) == 3                                    # header + image + depth
+        sch = Schema.from_message(rx.pending(), B, sizes)
+        assert sch.native and sch.column("image").shape == (90, 120, 4) and sch.column("depth").dtype == np.float32
+        ring = Ring(sch.slot_bytes, depth=1, device=None)
+        for first in (0, B):
+            slot, filled = ring.acquire(), 0
+            while filled < B:
+                rc, n = rx.fill(ring, slot, sch, filled, B - filled, 2000)
+                assert rc == N.BT_OK, N.last_error()
+                filled += n
+            view = ring.view(slot)
+            cols = {c.key: view[c.slot_off:c.slot_off + B * c.item_bytes].view(c.dtype).reshape((B,) + c.shape) for c in sch.columns}
+            for i in range(B):
+                want = items[first + i]
+                assert int(cols["frameid"][i]) == first + i and int(cols["btid"][i]) == 7
+                np.testing.assert_array_equal(cols["image"][i], want["image"])
+                np.testing.assert_array_equal(cols["depth"][i], want["depth"])
+        sender.join(10)
+        rx.close()
+
+
+def test_a_message_whose_consumer_vanished_before_it_started_goes_to_the_next_consumer():
+    """Finite pools: every message must reach somebody even when a consumer disconnects while idle."""
+    pools = [[pickle.dumps({"btid": 0, "frameid": i, "image": np.full((32, 32, 4), i, np.uint8)}, protocol=3) for i in range(6)]]
+    with btt.NativePublisher("tcp://127.0.0.1:*") as pub:
+        ctx = zmq.Context()
+        a, b = _pull(ctx, pub.addresses), _pull(ctx, pub.addresses)
+        _wait_peers(pub, 0, 2)
+        b.close()                                                  # leaves before anything is sent
+        time.sleep(0.1)
+        pub.start(pools, messages=30, threads=1)
+        got = [pickle.loads(a.recv())["frameid"] for _ in range(30)]
+        assert got == [i % 6 for i in range(30)]                   # all of them, in order, at the remaining consumer
+        assert pub.join(5)
+        a.close()
+        ctx.term()
